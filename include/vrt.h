@@ -1,0 +1,184 @@
+/* include/vrt.h -- C ABI of the B200-native replacement for VoxelRayTracer's per-pixel pass.
+ *
+ * The reference has no plugin/FFI interface: the hot path (res/shaders/voxel.glsl) is driven by the GL
+ * state that AppScene::Render() sets before ONE draw call (src/main.cpp:323-361).  Each entry point
+ * below replaces one piece of that GL-side interface; the citation says which.  All paths are
+ * relative to the reference tree.
+ *
+ * Conventions
+ *   - every function returns 0 (VRT_OK) or a negative VRT_E_* code; nothing aborts or throws.
+ *   - a vrt_ctx is bound to one CUDA device and is not thread-safe (the reference renders on one
+ *     GL thread); use one ctx per GPU.
+ *   - `stream` arguments are a cudaStream_t passed as void* (NULL = the legacy default stream).
+ *   - pixel rows are in GL order: row 0 is the BOTTOM scanline (FrameBuffer colour texture,
+ *     src/FrameBuffer.cpp:8-12); the atlas is given in GL memory order too (row 0 is t = 0).
+ *   - there is NO CPU fallback: without a usable CUDA device vrt_create() fails with
+ *     VRT_E_NO_DEVICE and nothing else can be called.
+ */
+#ifndef VRT_H_
+#define VRT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VRT_ABI_VERSION 1
+
+enum {
+  VRT_OK = 0,
+  VRT_E_INVALID = -1,      /* bad argument (null pointer, size not a power of two, tile outside frame ...) */
+  VRT_E_NO_DEVICE = -2,    /* no CUDA device / driver; there is no CPU fallback */
+  VRT_E_CUDA = -3,         /* a CUDA runtime call failed; vrt_last_error() has the text */
+  VRT_E_NOT_READY = -4,    /* render before grid (or atlas, for textured shading) upload */
+  VRT_E_OOM = -5
+};
+
+/* flags for vrt_params.flags */
+#define VRT_FLAG_COLOR_ONLY 0x1u /* the shader's `#define _COLOR_ONLY` variant (voxel.glsl:6,69-89,177-181,336-345) */
+#define VRT_FLAG_DEBUG_MAPS 0x2u /* also write the primary hit-voxel index map and the bounce-count map */
+#define VRT_FLAG_EXACT      0x4u /* literal float replay of the shader's DDA (bit-exact traversal); default is
+                                    the brick-skipping traversal, which may differ on grazing rays only */
+#define VRT_FLAG_COUNTERS   0x8u /* accumulate ray/step counters (vrt_get_counters); slower, for tests/roofline */
+#define VRT_FLAG_FLOAT_OUT  0x10u /* also keep an unquantised float32 RGBA frame for RMS checks */
+
+#define VRT_HIT_MISS 0xFFFFFFFFu
+
+/* Per-frame inputs == the uniforms AppScene::Render() sets (src/main.cpp:333-348; declared at
+ * voxel.glsl:14-25,463-465) plus the viewport (src/main.cpp:325) and, new here, the screen tile this
+ * call renders (for multi-GPU sharding; the reference always renders the full frame). */
+typedef struct vrt_params {
+  int32_t width, height;      /* full frame size in pixels: rayTraceFrameBuffer size (main.cpp:325,434-450) */
+  int32_t tile_x0, tile_y0;   /* tile rectangle inside the frame; 0,0,width,height renders everything */
+  int32_t tile_w, tile_h;
+  int32_t band_rows;          /* row-band interleave inside the tile: with band_count > 1 only bands */
+  int32_t band_count;         /*   b = (y - tile_y0) / band_rows with b % band_count == band_index are  */
+  int32_t band_index;         /*   rendered, stored compactly band after band.  0/1/0 = off.           */
+  float invPV[16];            /* u_PVInvMatrix, column-major as glUniformMatrix4fv(transpose=GL_FALSE) (main.cpp:333) */
+  int32_t size;               /* u_Size: voxels per chunk edge (main.cpp:335); must equal the uploaded grid's */
+  int32_t atlasSize;          /* u_AtlasSize (main.cpp:336) */
+  int32_t atlasTextureSize;   /* u_AtlasTextureSize (main.cpp:337) */
+  float sunDir[3];            /* u_SunDir (main.cpp:346-348); need not be unit length */
+  float time;                 /* u_Time: frame counter, 1 on the first frame (main.cpp:343-345) */
+  float rayNoise;             /* u_RayNoise (main.cpp:340) */
+  float reflectionNoise;      /* u_ReflectionNoise (main.cpp:341) */
+  float refractionNoise;      /* u_RefractionNoise (main.cpp:342) */
+  float maxRayLength;         /* u_MaxRayLength: default 100, never set by the host (voxel.glsl:17) */
+  int32_t maxReflections;     /* MAX_REFLECTIONS = 1 (voxel.glsl:4) */
+  int32_t maxTransparencies;  /* MAX_TRANSPARENCIES = 2 (voxel.glsl:5); maxReflections + maxTransparencies <= 7 */
+  uint32_t flags;             /* VRT_FLAG_* */
+} vrt_params;
+
+/* Counters accumulated by renders that carry VRT_FLAG_COUNTERS (reset by vrt_reset_counters).
+ * A "ray" is one RayMarch (voxel.glsl:302) or RayMarchShadow (voxel.glsl:259) invocation; a "step"
+ * is one iteration of their while loops (voxel.glsl:273,317) AS THE REFERENCE WOULD EXECUTE THEM. */
+typedef struct vrt_counters {
+  uint64_t primary_rays, secondary_rays, shadow_rays;
+  uint64_t march_steps, shadow_steps;   /* reference-equivalent steps (exact mode) */
+  uint64_t actual_steps;                /* loop iterations the kernel really executed (with skipping) */
+  uint64_t hits, tie_index3;            /* shaded hits; steps whose axis index was 3 (pin G1) */
+} vrt_counters;
+
+typedef struct vrt_ctx vrt_ctx;
+
+/* Fills defaults: full-frame tile, maxRayLength 100, maxReflections 1, maxTransparencies 2,
+ * noise 0, time 1, flags 0 (voxel.glsl:4-5,17; main.cpp:155-158). */
+void vrt_default_params(vrt_params* p, int width, int height, int size);
+
+int vrt_abi_version(void);
+
+/* Context = the GL context + shader program + the three texture objects of AppScene (main.cpp:160-320). */
+int vrt_create(int device, vrt_ctx** out);
+int vrt_destroy(vrt_ctx* ctx);
+const char* vrt_last_error(const vrt_ctx* ctx); /* never NULL; ctx may be NULL (global last error) */
+
+/* Replaces glTexImage3D(GL_TEXTURE_3D, GL_RED, size^3, GL_UNSIGNED_BYTE) (main.cpp:315-318).
+ * voxels[x + y*size + z*size*size] (main.cpp:227); copied; size must be a power of two, 8..2048.
+ * Triggers the on-device brick/occupancy repack. */
+int vrt_upload_grid(vrt_ctx* ctx, const uint8_t* voxels, int size);
+/* Same, with the grid already in device memory (e.g. filled by another kernel or broadcast by NCCL). */
+int vrt_upload_grid_device(vrt_ctx* ctx, const void* d_voxels, int size, void* stream);
+
+/* Replaces Atlas(atlasSize, textureSize) + 4 x AddTexture (main.cpp:177-183,187-193): the finished
+ * RGBA8 atlas image, atlasSize x atlasSize texels, GL memory order, sampled NEAREST. */
+int vrt_upload_atlas(vrt_ctx* ctx, const uint8_t* rgba8, int atlasSize, int textureSize);
+
+/* Replaces the draw at main.cpp:349-353 (vertex + fragment stage of voxel.glsl for every pixel of the
+ * tile).  Asynchronous on `stream`.  Output: RGBA8, tile rows compact, into the ctx-owned framebuffer
+ * (grown on demand like FrameBuffer::Resize, FrameBuffer.cpp:47-60). */
+int vrt_render(vrt_ctx* ctx, const vrt_params* p, void* stream);
+/* Same, into caller-provided DEVICE memory (>= vrt_tile_pixels(p)*4 bytes): a torch tensor, or another
+ * GPU's buffer mapped through P2P/IPC so that the frame is gathered by the render kernel's own stores. */
+int vrt_render_to(vrt_ctx* ctx, const vrt_params* p, void* d_rgba8, void* stream);
+/* Render + device->host copy + synchronise: what a host caller of the reference sees (frame in host memory). */
+int vrt_render_host(vrt_ctx* ctx, const vrt_params* p, uint8_t* host_rgba8, void* stream);
+
+/* Number of pixels a render with these params writes (tile and band selection applied). */
+int64_t vrt_tile_pixels(const vrt_params* p);
+
+/* FrameBuffer::GetTexture() (FrameBuffer.cpp:27-30): the device buffer the last vrt_render wrote. */
+int vrt_framebuffer_device(vrt_ctx* ctx, void** d_rgba8, size_t* bytes);
+/* Synchronises `ctx`'s last render stream and copies the last rendered tile to the host. */
+int vrt_read_framebuffer(vrt_ctx* ctx, uint8_t* host_rgba8, size_t bytes);
+/* After a render with VRT_FLAG_DEBUG_MAPS: hit[p] = x + y*size + z*size*size of the primary ray's hit
+ * voxel or VRT_HIT_MISS; bounces[p] = rays popped from the stack (voxel.glsl:436), 1..9. */
+int vrt_read_debug_maps(vrt_ctx* ctx, uint32_t* hit, uint8_t* bounces, size_t npix);
+/* After a render with VRT_FLAG_FLOAT_OUT: unquantised f_Color (voxel.glsl:451), 4 floats per pixel. */
+int vrt_read_float_frame(vrt_ctx* ctx, float* rgba_f32, size_t npix);
+
+int vrt_reset_counters(vrt_ctx* ctx);
+int vrt_get_counters(vrt_ctx* ctx, vrt_counters* out);
+
+/* Device time of the last render's kernel(s) in milliseconds (CUDA events on the render stream);
+ * replaces the GL_TIME_ELAPSED query at main.cpp:350-357.  Synchronises. */
+int vrt_last_render_ms(vrt_ctx* ctx, float* ms);
+/* Number of kernels launched by this ctx since creation (for bench accounting). */
+int64_t vrt_kernel_launches(const vrt_ctx* ctx);
+
+/* ---- brick layout inspection (tests) ---- */
+typedef struct vrt_grid_info {
+  int32_t size, brick_dim, bricks_per_axis;
+  int64_t bricks_total, bricks_occupied, voxels_occupied;
+} vrt_grid_info;
+int vrt_grid_info_get(vrt_ctx* ctx, vrt_grid_info* out);
+
+/* ---- temporal accumulation pass (res/shaders/temporal.glsl:13-19; main.cpp:363-376,388-393) ----
+ * acc = alpha * new + (1 - alpha) * acc on RGBA8 device buffers, n pixels. */
+int vrt_temporal_blend(vrt_ctx* ctx, const void* d_new_rgba8, void* d_acc_rgba8, int64_t npix, float alpha, void* stream);
+
+/* ---- cross-process framebuffer sharing for the fused render+gather path (CUDA IPC) ---- */
+#define VRT_IPC_HANDLE_BYTES 64
+int vrt_ipc_alloc_frame(vrt_ctx* ctx, size_t bytes, void** d_ptr, uint8_t handle[VRT_IPC_HANDLE_BYTES]);
+int vrt_ipc_open(vrt_ctx* ctx, const uint8_t handle[VRT_IPC_HANDLE_BYTES], void** d_ptr);
+int vrt_ipc_close(vrt_ctx* ctx, void* d_ptr);
+
+/* ---- host-side scene/camera helpers (no GPU needed) ----
+ * Stand-ins for the parts of the un-vendored Greet engine that feed the path, with the conventions
+ * written in DESIGN.md ("engine stand-ins"). */
+
+/* Grid fillers following src/main.cpp:219-288.  heightmap: size*size floats in [0,1), index x + z*size
+ * (terrain only; NULL otherwise). glass_walls: 1 = also run the glass-wall block that the reference
+ * guards with size <= 64 (main.cpp:233-249) regardless of size; 0 = follow the guard. */
+enum { VRT_SCENE_TERRAIN = 0, VRT_SCENE_GLASS_CUBE = 1, VRT_SCENE_REFRACTION = 2, VRT_SCENE_SYNTHETIC = 3 };
+int vrt_scene_fill(int kind, int size, const float* heightmap, int glass_walls, uint32_t seed, uint8_t* voxels);
+/* Seeded value-noise heightmap in [0, 0.999], stand-in for Greet::Noise::GenNoise (main.cpp:185,195). */
+int vrt_noise_heightmap(int size, uint32_t seed, int octaves, float persistence, float* out);
+/* Procedural RGBA8 tiles + packing in the reference's order stone, dirt, glass, grass (main.cpp:179-182);
+ * out is atlasSize*atlasSize*4 bytes in GL memory order, atlasSize = 2*textureSize. */
+int vrt_atlas_synthetic(int textureSize, uint32_t seed, uint8_t* out_rgba8);
+/* Packs 4 caller-supplied textureSize^2 RGBA8 tiles (image order, row 0 = top) the same way. */
+int vrt_atlas_pack(const uint8_t* stone, const uint8_t* dirt, const uint8_t* glass, const uint8_t* grass,
+                   int textureSize, uint8_t* out_rgba8);
+/* Cam (main.cpp:14-77): view = RotX(-rot.x) * RotY(-rot.y) * Translate(-pos); invPV = inverse(P * V) with
+ * P = Perspective(aspect, fovDeg, near, far).  Angles in radians.  out: 16 floats, column-major. */
+int vrt_camera_invpv(const float pos[3], const float rot[3], float aspect, float fov_deg, float z_near, float z_far,
+                     float out_invPV[16]);
+/* Sun direction from the day/night cycle (main.cpp:346-348). */
+int vrt_sun_dir(float timeOfDay, float dayTime, float out[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VRT_H_ */
