@@ -137,12 +137,23 @@ int vrt_last_render_ms(vrt_ctx* ctx, float* ms);
 /* Number of kernels launched by this ctx since creation (for bench accounting). */
 int64_t vrt_kernel_launches(const vrt_ctx* ctx);
 
-/* ---- brick layout inspection (tests) ---- */
+/* ---- repacked grid inspection (tests) ----
+ * The upload repacks the chunk into traversal cells: a (size+2)^3 array of uint16 with a one-cell border,
+ * cell = (emptyRadius << 8) | voxelByte, emptyRadius = Chebyshev distance to the nearest occupied voxel or
+ * border cell (0 for occupied and border cells), capped at radius_cap.  Index (x+1) + (y+1)*pitch + (z+1)*pitch^2. */
 typedef struct vrt_grid_info {
-  int32_t size, brick_dim, bricks_per_axis;
-  int64_t bricks_total, bricks_occupied, voxels_occupied;
+  int32_t size, pitch, radius_cap, reserved;
+  int64_t cells_total, voxels_occupied;
 } vrt_grid_info;
 int vrt_grid_info_get(vrt_ctx* ctx, vrt_grid_info* out);
+int vrt_read_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count); /* count must be (size+2)^3 */
+
+/* ---- memory helpers for callers without a CUDA toolchain (ctypes, cgo ...) ---- */
+int vrt_host_alloc(vrt_ctx* ctx, size_t bytes, void** out);   /* pinned host memory */
+int vrt_host_free(vrt_ctx* ctx, void* p);
+int vrt_device_alloc(vrt_ctx* ctx, size_t bytes, void** out);
+int vrt_device_free(vrt_ctx* ctx, void* p);
+int vrt_synchronize(vrt_ctx* ctx, void* stream);
 
 /* ---- temporal accumulation pass (res/shaders/temporal.glsl:13-19; main.cpp:363-376,388-393) ----
  * acc = alpha * new + (1 - alpha) * acc on RGBA8 device buffers, n pixels. */

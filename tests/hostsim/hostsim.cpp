@@ -1,0 +1,137 @@
+// tests/hostsim/hostsim.cpp -- TEST INFRASTRUCTURE ONLY.
+//
+// Compiles the product's device headers (voxelraytracer_b200/csrc/rt_*.cuh) for the HOST, so that the
+// kernels' per-pixel logic can be checked against the oracle on a machine without a GPU.  The headers
+// use explicit operation order and are built with -ffp-contract=off here and -fmad=false under nvcc,
+// so what this predicts is what the GPU computes (up to powf's last ulp in colours).
+// This library is never loaded by the product (voxelraytracer_b200/ has no reference to it) and is not
+// a fallback: vrt_create() fails without a CUDA device.
+//
+// Build: g++ -std=c++17 -O2 -ffp-contract=off -fno-fast-math -fPIC -shared -pthread -x c++ hostsim.cpp
+#include "../../voxelraytracer_b200/csrc/rt_trace_exact.cuh"
+#include "../../voxelraytracer_b200/csrc/rt_trace_fast.cuh"
+
+#include <atomic>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+using namespace vrt;
+
+extern "C" {
+
+// CPU statement of the repack (voxelraytracer_b200/csrc/repack.cu): padded (n+2)^3 uint16 cells,
+// low byte = voxel, high byte = Chebyshev distance to the nearest occupied-or-border cell (cap 255).
+int hostsim_build_cells(const uint8_t* grid, int n, uint16_t* cells) {
+  const int P = n + 2;
+  std::vector<uint8_t> a((size_t)n * n * n), b((size_t)n * n * n);
+  auto at = [n](int x, int y, int z) { return (size_t)x + (size_t)y * n + (size_t)z * n * n; };
+  auto cap = [](int v) { return (uint8_t)(v > 255 ? 255 : v); };
+  // pass x: distance along the row to the nearest occupied voxel or to the border cell (-1 or n)
+  for (int z = 0; z < n; z++)
+    for (int y = 0; y < n; y++) {
+      int d = 0;  // distance to the last obstacle seen; the border cell at x = -1 is an obstacle
+      for (int x = 0; x < n; x++) { d = grid[at(x, y, z)] ? 0 : d + 1; a[at(x, y, z)] = cap(d); }
+      d = 0;
+      for (int x = n - 1; x >= 0; x--) { d = grid[at(x, y, z)] ? 0 : d + 1; if (d < a[at(x, y, z)]) a[at(x, y, z)] = cap(d); }
+    }
+  // pass y, z: D(y) = min_k max(|k|, D'(y+k)), border at distance y+1 / n-y
+  for (int pass = 0; pass < 2; pass++) {
+    const std::vector<uint8_t>& src = pass == 0 ? a : b;
+    std::vector<uint8_t>& dst = pass == 0 ? b : a;
+    for (int z = 0; z < n; z++)
+      for (int y = 0; y < n; y++)
+        for (int x = 0; x < n; x++) {
+          int c = pass == 0 ? y : z;
+          int best = src[at(x, y, z)];
+          int edge = c + 1 < n - c ? c + 1 : n - c;
+          if (edge < best) best = edge;
+          for (int k = 1; k < best; k++) {
+            int lo = c - k, hi = c + k;
+            if (lo >= 0) { int v = pass == 0 ? src[at(x, lo, z)] : src[at(x, y, lo)]; int m = v > k ? v : k; if (m < best) best = m; }
+            if (hi < n) { int v = pass == 0 ? src[at(x, hi, z)] : src[at(x, y, hi)]; int m = v > k ? v : k; if (m < best) best = m; }
+          }
+          dst[at(x, y, z)] = cap(best);
+        }
+  }
+  std::memset(cells, 0, (size_t)P * P * P * sizeof(uint16_t));
+  for (int z = 0; z < n; z++)
+    for (int y = 0; y < n; y++)
+      for (int x = 0; x < n; x++) {
+        uint8_t v = grid[at(x, y, z)];
+        uint8_t r = v ? 0 : a[at(x, y, z)];
+        cells[(size_t)(x + 1) + (size_t)(y + 1) * P + (size_t)(z + 1) * P * P] = (uint16_t)((r << 8) | v);
+      }
+  return 0;
+}
+
+}  // extern "C"
+
+template <class Tracer, bool FLAT>
+static void render_rows(const FrameArgs& f, std::atomic<int>& next, float* out_f32, uint8_t* out_rgba8, uint32_t* out_hit,
+                        uint8_t* out_bounces, uint64_t* counters) {
+  uint64_t local[CNT_N] = {0};
+  for (;;) {
+    int ly = next.fetch_add(1);
+    if (ly >= f.rows_local) break;
+    int py = frame_row(f.p, ly);
+    for (int lx = 0; lx < f.p.tile_w; lx++) {
+      PixelCtx<FLAT, true> cx(f);
+      PixelResult r = shade_pixel<Tracer, FLAT, true>(cx, f.p.tile_x0 + lx, py);
+      size_t o = (size_t)ly * f.p.tile_w + lx;
+      if (out_f32) std::memcpy(out_f32 + o * 4, r.rgba, 16);
+      if (out_rgba8) {
+        out_rgba8[o * 4 + 0] = quantize_unorm8(r.rgba[0]); out_rgba8[o * 4 + 1] = quantize_unorm8(r.rgba[1]);
+        out_rgba8[o * 4 + 2] = quantize_unorm8(r.rgba[2]); out_rgba8[o * 4 + 3] = 255;
+      }
+      if (out_hit) out_hit[o] = r.hit;
+      if (out_bounces) out_bounces[o] = (uint8_t)r.bounces;
+      for (int i = 0; i < CNT_N; i++) local[i] += cx.cnt.v[i];
+    }
+  }
+  static std::atomic_flag lock = ATOMIC_FLAG_INIT;
+  while (lock.test_and_set()) {}
+  for (int i = 0; i < CNT_N; i++) counters[i] += local[i];
+  lock.clear();
+}
+
+extern "C" {
+
+// mode: 0 = exact tracer, 1 = fast tracer (cells required).  counters: CNT_N (8) uint64, optional.
+int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cells, const uint8_t* atlas, int mode, float* out_f32,
+                   uint8_t* out_rgba8, uint32_t* out_hit, uint8_t* out_bounces, uint64_t* counters, int nthreads) {
+  if (!p || !grid) return -1;
+  if (mode == 1 && !cells) return -1;
+  FrameArgs f;
+  std::memset(&f, 0, sizeof(f));
+  f.p = *p;
+  f.grid = grid; f.cells = cells; f.atlas = atlas;
+  f.sun_unit = normalize3(mk3(p->sunDir[0], p->sunDir[1], p->sunDir[2]));
+  f.fsize = (float)p->size;
+  f.day = gmax(p->sunDir[1], 0.0f);
+  f.log2n = 0;
+  while ((1 << f.log2n) < p->size) f.log2n++;
+  if ((1 << f.log2n) != p->size) return -1;
+  f.rows_local = (int)(vrt_tile_pixels(p) / p->tile_w);
+  bool flat = (p->flags & VRT_FLAG_COLOR_ONLY) != 0;
+  uint64_t cnt[CNT_N] = {0};
+  std::atomic<int> next(0);
+  auto work = [&]() {
+    if (mode == 0) {
+      if (flat) render_rows<ExactTracer<true, true>, true>(f, next, out_f32, out_rgba8, out_hit, out_bounces, cnt);
+      else render_rows<ExactTracer<false, true>, false>(f, next, out_f32, out_rgba8, out_hit, out_bounces, cnt);
+    } else {
+      if (flat) render_rows<FastTracer<true, true>, true>(f, next, out_f32, out_rgba8, out_hit, out_bounces, cnt);
+      else render_rows<FastTracer<false, true>, false>(f, next, out_f32, out_rgba8, out_hit, out_bounces, cnt);
+    }
+  };
+  if (nthreads < 1) nthreads = 1;
+  std::vector<std::thread> th;
+  for (int i = 1; i < nthreads; i++) th.emplace_back(work);
+  work();
+  for (auto& t : th) t.join();
+  if (counters) std::memcpy(counters, cnt, sizeof(cnt));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,71 @@
+// kernels.cu -- the per-pixel kernels (sm_100a).  Compiled with -fmad=false (see rt_common.cuh).
+//
+// One thread per pixel.  A warp owns an 8x4 pixel patch (x fastest) so that its 32 rays stay within a
+// few voxels of each other and hit the same 128-byte lines of the cell array; a CTA of 4 warps owns a
+// 16x8 patch.  Replaces the draw at src/main.cpp:349-353 (vertex + fragment stage of voxel.glsl).
+#include "vrt_internal.h"
+#include "rt_trace_exact.cuh"
+#include "rt_trace_fast.cuh"
+
+namespace vrt {
+
+constexpr int kWarpW = 8, kWarpH = 4;       // pixels per warp patch
+constexpr int kCtaWarpsX = 2, kCtaWarpsY = 2;
+constexpr int kCtaW = kWarpW * kCtaWarpsX, kCtaH = kWarpH * kCtaWarpsY;
+constexpr int kThreads = 32 * kCtaWarpsX * kCtaWarpsY;
+
+template <class Tracer, bool FLAT, bool DEBUG>
+__device__ __forceinline__ void render_one(const FrameArgs& f, int lx, int ly) {
+  PixelCtx<FLAT, DEBUG> cx(f);
+  const bool live = lx < f.p.tile_w && ly < f.rows_local;
+  if (live) {
+    const int px = f.p.tile_x0 + lx, py = frame_row(f.p, ly);
+    PixelResult r = shade_pixel<Tracer, FLAT, DEBUG>(cx, px, py);
+    const size_t o = (size_t)ly * (size_t)f.p.tile_w + (size_t)lx;
+    uchar4 q;
+    q.x = quantize_unorm8(r.rgba[0]); q.y = quantize_unorm8(r.rgba[1]); q.z = quantize_unorm8(r.rgba[2]); q.w = 255;
+    reinterpret_cast<uchar4*>(f.out_rgba8)[o] = q;
+    if (DEBUG) {
+      if (f.out_f32) reinterpret_cast<float4*>(f.out_f32)[o] = make_float4(r.rgba[0], r.rgba[1], r.rgba[2], r.rgba[3]);
+      if (f.out_hit) f.out_hit[o] = r.hit;
+      if (f.out_bounces) f.out_bounces[o] = (uint8_t)r.bounces;
+    }
+  }
+  if (DEBUG) {
+    if (f.counters) {
+      // warp-aggregate, one atomic per counter per warp (all 32 lanes reach this point)
+#pragma unroll
+      for (int i = 0; i < CNT_N; i++) {
+        unsigned v = __reduce_add_sync(0xFFFFFFFFu, live ? cx.cnt.v[i] : 0u);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(f.counters + i, (unsigned long long)v);
+      }
+    }
+  }
+}
+
+template <class Tracer, bool FLAT, bool DEBUG>
+__global__ void __launch_bounds__(kThreads) render_kernel(const __grid_constant__ FrameArgs f) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int lx = blockIdx.x * kCtaW + (warp % kCtaWarpsX) * kWarpW + (lane & (kWarpW - 1));
+  const int ly = blockIdx.y * kCtaH + (warp / kCtaWarpsX) * kWarpH + (lane / kWarpW);
+  render_one<Tracer, FLAT, DEBUG>(f, lx, ly);
+}
+
+template <class Tracer, bool FLAT, bool DEBUG>
+static cudaError_t launch_variant(const FrameArgs& a, cudaStream_t s) {
+  dim3 grid((unsigned)((a.p.tile_w + kCtaW - 1) / kCtaW), (unsigned)((a.rows_local + kCtaH - 1) / kCtaH));
+  if (grid.x == 0 || grid.y == 0) return cudaSuccess;
+  render_kernel<Tracer, FLAT, DEBUG><<<grid, kThreads, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_render(const FrameArgs& a, bool exact, bool flat, bool debug, cudaStream_t s) {
+  if (exact) {
+    if (flat) return debug ? launch_variant<ExactTracer<true, true>, true, true>(a, s) : launch_variant<ExactTracer<true, false>, true, false>(a, s);
+    return debug ? launch_variant<ExactTracer<false, true>, false, true>(a, s) : launch_variant<ExactTracer<false, false>, false, false>(a, s);
+  }
+  if (flat) return debug ? launch_variant<FastTracer<true, true>, true, true>(a, s) : launch_variant<FastTracer<true, false>, true, false>(a, s);
+  return debug ? launch_variant<FastTracer<false, true>, false, true>(a, s) : launch_variant<FastTracer<false, false>, false, false>(a, s);
+}
+
+}  // namespace vrt

@@ -1,0 +1,93 @@
+// repack.cu -- K2: raw R8 chunk (what glTexImage3D received, src/main.cpp:315-318) -> traversal cells.
+//
+// Output layout (consumed by rt_trace_fast.cuh): (n+2)^3 uint16, one-cell border of 0x0000,
+//   cell = (emptyRadius << 8) | voxelByte, emptyRadius = Chebyshev distance to the nearest occupied voxel
+//   or border cell, capped; 0 for occupied cells.
+// The L-infinity distance transform is separable: D = min over z' of max(|z-z'|, min over y' of
+// max(|y-y'|, dx(x, y', z'))).  Each pass is one thread per voxel scanning outward along one axis until the
+// ring radius reaches the best value found so far, so the work per voxel is O(result), and every pass is
+// HBM/L2 streaming with x as the fastest thread index (coalesced rows).
+#include "vrt_internal.h"
+
+namespace vrt {
+
+__device__ __forceinline__ int imin(int a, int b) { return a < b ? a : b; }
+__device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
+
+// pass 0 (axis x) reads occupancy from the raw grid; passes 1, 2 (axes y, z) read the previous pass.
+template <int AXIS>
+__global__ void __launch_bounds__(256) distance_pass(const uint8_t* __restrict__ grid, const uint8_t* __restrict__ src,
+                                                      uint8_t* __restrict__ dst, int n, int log2n, int cap) {
+  const size_t total = (size_t)n << (2 * log2n);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i & (size_t)(n - 1)), y = (int)((i >> log2n) & (size_t)(n - 1)), z = (int)(i >> (2 * log2n));
+    const int c = AXIS == 0 ? x : (AXIS == 1 ? y : z);
+    const size_t stride = AXIS == 0 ? 1 : (AXIS == 1 ? (size_t)n : (size_t)n * n);
+    int best;
+    if (AXIS == 0) {
+      best = __ldg(grid + i) ? 0 : cap;
+    } else {
+      best = __ldg(src + i);
+    }
+    best = imin(best, imin(c + 1, n - c));  // the border cells at -1 and n are obstacles
+    for (int k = 1; k < best; k++) {
+      // ring k: both neighbours at distance k are inside the grid because k < best <= distance to the border
+      int lo, hi;
+      if (AXIS == 0) {
+        lo = __ldg(grid + i - (size_t)k) ? 0 : cap;
+        hi = __ldg(grid + i + (size_t)k) ? 0 : cap;
+      } else {
+        lo = __ldg(src + i - (size_t)k * stride);
+        hi = __ldg(src + i + (size_t)k * stride);
+      }
+      best = imin(best, imax(k, imin(lo, hi)));
+    }
+    dst[i] = (uint8_t)best;
+  }
+}
+
+__global__ void __launch_bounds__(256) pack_cells(const uint8_t* __restrict__ grid, const uint8_t* __restrict__ radius,
+                                                   uint16_t* __restrict__ cells, int n, int log2n, unsigned long long* stats) {
+  const int P = n + 2;
+  const size_t total = (size_t)P * P * P;
+  unsigned occupied = 0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % P) - 1, y = (int)((i / P) % P) - 1, z = (int)(i / ((size_t)P * P)) - 1;
+    uint16_t v = 0;
+    if ((unsigned)x < (unsigned)n && (unsigned)y < (unsigned)n && (unsigned)z < (unsigned)n) {
+      const size_t g = (size_t)x + ((size_t)y << log2n) + ((size_t)z << (2 * log2n));
+      const unsigned b = __ldg(grid + g);
+      const unsigned r = b ? 0u : (unsigned)__ldg(radius + g);
+      v = (uint16_t)((r << 8) | b);
+      occupied += b ? 1u : 0u;
+    }
+    cells[i] = v;
+  }
+  if (stats) {
+    unsigned w = __reduce_add_sync(0xFFFFFFFFu, occupied);
+    if ((threadIdx.x & 31) == 0 && w) atomicAdd(stats, (unsigned long long)w);
+  }
+}
+
+cudaError_t launch_repack(const uint8_t* d_grid, int n, int radius_cap, uint8_t* tmp_a, uint8_t* tmp_b, uint16_t* d_cells,
+                          unsigned long long* d_stats, cudaStream_t stream, int* launches) {
+  int log2n = 0;
+  while ((1 << log2n) < n) log2n++;
+  const size_t total = (size_t)n * n * n;
+  // grid-stride with enough CTAs to fill 148 SMs several times over; capped so the launch stays small
+  size_t want = (total + 255) / 256;
+  unsigned blocks = (unsigned)(want > 148u * 64u ? 148u * 64u : want);
+  if (blocks == 0) blocks = 1;
+  int cap = radius_cap < 1 ? 1 : (radius_cap > 255 ? 255 : radius_cap);
+  distance_pass<0><<<blocks, 256, 0, stream>>>(d_grid, nullptr, tmp_a, n, log2n, cap);
+  distance_pass<1><<<blocks, 256, 0, stream>>>(d_grid, tmp_a, tmp_b, n, log2n, cap);
+  distance_pass<2><<<blocks, 256, 0, stream>>>(d_grid, tmp_b, tmp_a, n, log2n, cap);
+  const size_t ptotal = (size_t)(n + 2) * (n + 2) * (n + 2);
+  size_t pwant = (ptotal + 255) / 256;
+  unsigned pblocks = (unsigned)(pwant > 148u * 64u ? 148u * 64u : pwant);
+  pack_cells<<<pblocks, 256, 0, stream>>>(d_grid, tmp_a, d_cells, n, log2n, d_stats);
+  if (launches) *launches = 4;
+  return cudaGetLastError();
+}
+
+}  // namespace vrt

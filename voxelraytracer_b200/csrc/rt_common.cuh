@@ -1,0 +1,172 @@
+// rt_common.cuh -- shared device-side definitions for the per-pixel pass (sm_100a).
+//
+// All float arithmetic in this directory is written with EXPLICIT operation order and explicit fmaf():
+// the translation units are compiled with -fmad=false, so a*b+c never contracts silently.  That is what
+// makes the exact kernel's traversal bit-identical with the CPU oracle (SURVEY.md H1 / pin G9), and it
+// lets tests/hostsim compile the very same headers for the host to predict GPU results without a GPU.
+#pragma once
+#include <stdint.h>
+#include <math.h>
+
+#include "../../include/vrt.h"
+
+#if defined(__CUDACC__)
+#define VRT_HD __host__ __device__ __forceinline__
+#define VRT_D __device__ __forceinline__
+#else
+#define VRT_HD inline
+#define VRT_D inline
+#endif
+
+namespace vrt {
+
+struct V3 { float x, y, z; };
+
+VRT_HD V3 mk3(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
+VRT_HD float vget(const V3& v, int a) { return a == 0 ? v.x : (a == 1 ? v.y : v.z); }
+VRT_HD void vset(V3& v, int a, float s) { if (a == 0) v.x = s; else if (a == 1) v.y = s; else v.z = s; }
+
+// GLSL built-ins with the pins of SURVEY.md 8(a'): dot = ((xx + yy) + zz); normalize = v / sqrt(dot) (G7)
+VRT_HD float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+VRT_HD V3 normalize3(V3 v) { float l = sqrtf(dot3(v, v)); return mk3(v.x / l, v.y / l, v.z / l); }
+VRT_HD float sign1(float x) { return x > 0.0f ? 1.0f : (x < 0.0f ? -1.0f : 0.0f); }
+VRT_HD float gmin(float x, float y) { return y < x ? y : x; }
+VRT_HD float gmax(float x, float y) { return x < y ? y : x; }
+VRT_HD V3 reflect3(V3 I, V3 N) { float s = 2.0f * dot3(N, I); return mk3(I.x - s * N.x, I.y - s * N.y, I.z - s * N.z); }
+VRT_HD V3 mix3(V3 x, V3 y, float a) {
+  float b = 1.0f - a;
+  return mk3(x.x * b + y.x * a, x.y * b + y.y * a, x.z * b + y.z * a);
+}
+
+VRT_HD uint32_t f2u(float f) {
+#if defined(__CUDA_ARCH__)
+  return __float_as_uint(f);
+#else
+  union { float f; uint32_t u; } c; c.f = f; return c.u;
+#endif
+}
+VRT_HD float u2f(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+  return __uint_as_float(u);
+#else
+  union { float f; uint32_t u; } c; c.u = u; return c.f;
+#endif
+}
+
+// voxel.glsl:98-130 -- Jenkins one-at-a-time round, uvec4 combiner, mantissa trick
+VRT_HD uint32_t oaat(uint32_t x) {
+  x += x << 10; x ^= x >> 6; x += x << 3; x ^= x >> 11; x += x << 15;
+  return x;
+}
+VRT_HD float random01(float a, float b, float c, float d) {
+  uint32_t h = oaat(f2u(a) ^ oaat(f2u(b)) ^ oaat(f2u(c)) ^ oaat(f2u(d)));
+  return u2f((h & 0x007FFFFFu) | 0x3F800000u) - 1.0f;
+}
+// voxel.glsl:132-140
+VRT_HD V3 randomize_direction(V3 dir, V3 pos, float randomness, float seed) {
+  float vx = (pos.x + dir.x) + seed, vy = (pos.y + dir.y) + seed, vz = (pos.z + dir.z) + seed;
+  float rx = random01(vx, vy, vz, 0.0f + seed);
+  float ry = random01(vx, vy, vz, 0.5f + seed);
+  float rz = random01(vx, vy, vz, 1.0f + seed);
+  return normalize3(mk3(dir.x + (rx - 0.5f) * randomness, dir.y + (ry - 0.5f) * randomness, dir.z + (rz - 0.5f) * randomness));
+}
+
+// voxel.glsl:50-89 -- the two material tables, as functions of the clamped material index min(byte, 3)
+struct MatProps { float refr, kd, ks, ke; int tx, ty; bool transparent, reflective; };
+
+template <bool FLAT>
+VRT_HD MatProps material_of(int byte) {
+  int i = byte > 3 ? 3 : byte;
+  MatProps m;
+  m.refr = i == 2 ? 1.5f : 1.0f;
+  m.transparent = (i == 0) | (i == 2);
+  m.reflective = i == 2;
+  m.kd = i == 0 ? 0.0f : (i == 2 ? 1.0f : 0.4f);
+  if (FLAT) {
+    m.ks = i == 0 ? 0.0f : (i == 2 ? 1.0f : 0.2f);
+    m.ke = i == 0 ? 0.0f : (i == 2 ? 1.0f : 10.0f);
+    m.tx = 0; m.ty = 0;
+  } else {
+    m.ks = i == 0 ? 0.0f : (i == 1 ? 0.6f : (i == 2 ? 1.0f : 0.4f));
+    m.ke = i == 0 ? 0.0f : (i == 1 ? 60.0f : (i == 2 ? 0.3f : 20.0f));
+    m.tx = i == 3 ? 1 : 0;
+    m.ty = i >= 2 ? 1 : 0;
+  }
+  return m;
+}
+VRT_HD bool is_transparent(int byte) { return byte == 0 || byte == 2; }
+VRT_HD float refractivity(int byte) { return byte == 2 ? 1.5f : 1.0f; }
+
+// _COLOR_ONLY material colours (voxel.glsl:82-87)
+VRT_HD void flat_color(int byte, float c[4]) {
+  int i = byte > 3 ? 3 : byte;
+  if (i == 1) { c[0] = 0.5f; c[1] = 0.5f; c[2] = 0.5f; c[3] = 1.0f; }
+  else if (i == 3) { c[0] = 0.05f; c[1] = 0.5f; c[2] = 0.1f; c[3] = 1.0f; }
+  else { c[0] = 0.0f; c[1] = 0.0f; c[2] = 0.0f; c[3] = 0.0f; }
+}
+
+struct Ray {
+  V3 pos, dir;
+  float len, energy;
+  int medium;          // byte of the voxel the ray is inside (the shader's ray.voxel * 255)
+  int nrefl, ntrans;
+  // Not in the shader: where the ray starts.  face_axis >= 0 means `pos` lies on a voxel face normal to
+  // that axis (the ray was spawned at a hit) and face_nsign is that face's normal sign, i.e. the side the
+  // parent ray came from.  The exact tracer ignores both; the fast tracer uses them to pick the start cell
+  // from integers instead of from the last ulp of pos.
+  int face_axis;
+  float face_nsign;
+};
+
+struct Hit {
+  bool found;
+  int voxel;           // byte
+  V3 point;
+  float len;
+  int axis;            // 0,1,2: axis of the face that was crossed
+  float nsign;         // normal[axis] = -sign(dir[axis])
+  float u, v;          // atlas coordinates (textured variant)
+  uint32_t cell;       // x + y*n + z*n*n
+};
+
+// Everything a pixel needs, passed by value as a __grid_constant__ kernel parameter.
+struct FrameArgs {
+  vrt_params p;
+  const uint8_t* grid;      // raw R8 voxels, x + y*n + z*n*n (what glTexImage3D received, main.cpp:318)
+  const uint16_t* cells;    // repacked: (emptyRadius << 8) | voxelByte, (n+2)^3 with a one-cell border (rt_trace_fast.cuh)
+  const uint8_t* atlas;     // RGBA8, atlasSize^2, GL memory order
+  uint8_t* out_rgba8;       // tile, compact rows
+  float* out_f32;           // optional unquantised frame
+  uint32_t* out_hit;        // optional debug maps
+  uint8_t* out_bounces;
+  unsigned long long* counters;  // optional vrt_counters image (8 x u64)
+  V3 sun_unit;              // normalize(u_SunDir)
+  float fsize;              // (float)u_Size
+  float day;                // max(u_SunDir.y, 0)
+  int rows_local;           // number of compact rows this launch writes
+  int log2n;
+};
+
+// local row -> frame row (band interleave, see include/vrt.h)
+VRT_HD int frame_row(const vrt_params& p, int ly) {
+  if (p.band_count <= 1) return p.tile_y0 + ly;
+  int br = p.band_rows > 0 ? p.band_rows : 1;
+  int lb = ly / br;
+  return p.tile_y0 + (lb * p.band_count + p.band_index) * br + (ly - lb * br);
+}
+
+VRT_HD uint8_t quantize_unorm8(float c) {  // pin G6: round(clamp(c,0,1)*255); NaN -> 0
+  if (!(c > 0.0f)) return 0;
+  if (c > 1.0f) c = 1.0f;
+  return (uint8_t)floorf(c * 255.0f + 0.5f);
+}
+
+enum { CNT_PRIMARY = 0, CNT_SECONDARY, CNT_SHADOW, CNT_MARCH_STEPS, CNT_SHADOW_STEPS, CNT_ACTUAL_STEPS, CNT_HITS, CNT_TIE3, CNT_N };
+
+// Per-thread counters, flushed once per pixel (only instantiated when counting is requested).
+struct PixelCounters {
+  uint32_t v[CNT_N];
+  VRT_HD void clear() { for (int i = 0; i < CNT_N; i++) v[i] = 0; }
+};
+
+}  // namespace vrt

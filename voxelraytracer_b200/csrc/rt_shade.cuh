@@ -1,0 +1,221 @@
+// rt_shade.cuh -- ray generation, bounce rays, shading and the per-pixel ray-stack loop.
+// Restates voxel.glsl:144-246 (voxel/material/colour access, shadow/reflection/refraction ray
+// construction), :386-452 (sky, TraceWithShadow, main) and :467-475 (vertex stage), with the pins
+// G1-G13.  The DDA itself is supplied by a Tracer policy (rt_trace_exact.cuh / rt_trace_fast.cuh).
+#pragma once
+#include "rt_common.cuh"
+
+namespace vrt {
+
+template <bool FLAT, bool COUNT>
+struct PixelCtx {
+  const FrameArgs& f;
+  PixelCounters cnt;
+  VRT_HD explicit PixelCtx(const FrameArgs& fa) : f(fa) { if (COUNT) cnt.clear(); }
+  VRT_HD void count(int which, uint32_t n = 1) { if (COUNT) cnt.v[which] += n; }
+
+  // GetVoxel (voxel.glsl:149-154) with REPEAT/NEAREST texel selection (G4).  u_Size is a power of two, so
+  // coord/size*size == coord exactly and floor(coord) & (n-1) is the wrapped texel.
+  VRT_HD int voxel_at(float x, float y, float z, uint32_t* cell) const {
+    float s = f.fsize;
+    if (x < 0.0f || y < 0.0f || z < 0.0f || x > s || y > s || z > s) return 0;
+    int m = f.p.size - 1;
+    int i = ((int)floorf(x)) & m, j = ((int)floorf(y)) & m, k = ((int)floorf(z)) & m;
+    uint32_t idx = (uint32_t)i + ((uint32_t)j << f.log2n) + ((uint32_t)k << (2 * f.log2n));
+    if (cell) *cell = idx;
+#if defined(__CUDA_ARCH__)
+    return __ldg(f.grid + idx);
+#else
+    return f.grid[idx];
+#endif
+  }
+
+  // GetColor (voxel.glsl:174-182); atlas sampled NEAREST, clamp-to-edge (G13)
+  VRT_HD void color_of(const Hit& h, float c[4]) const {
+    if (FLAT) { flat_color(h.voxel, c); return; }
+    int n = f.p.atlasSize;
+    int i = (int)floorf(h.u * (float)n), j = (int)floorf(h.v * (float)n);
+    i = i < 0 ? 0 : (i > n - 1 ? n - 1 : i);
+    j = j < 0 ? 0 : (j > n - 1 ? n - 1 : j);
+#if defined(__CUDA_ARCH__)
+    uchar4 t = __ldg(reinterpret_cast<const uchar4*>(f.atlas) + ((size_t)j * n + i));
+    c[0] = (float)t.x / 255.0f; c[1] = (float)t.y / 255.0f; c[2] = (float)t.z / 255.0f; c[3] = (float)t.w / 255.0f;
+#else
+    const uint8_t* t = f.atlas + ((size_t)j * n + i) * 4;
+    for (int k = 0; k < 4; k++) c[k] = (float)t[k] / 255.0f;
+#endif
+  }
+
+  // GetTextureCoordinate (voxel.glsl:167-172) for the face `axis` at point q: plane axes x-face -> (z,y),
+  // y-face -> (x,z), z-face -> (x,y) (voxel.glsl:93,337-342)
+  VRT_HD void tex_coord(const V3& q, int axis, int voxel, float* u, float* v) const {
+    if (FLAT) { *u = 0.0f; *v = 0.0f; return; }
+    float a = axis == 0 ? q.z : q.x;
+    float b = axis == 0 ? q.y : (axis == 1 ? q.z : q.y);
+    MatProps m = material_of<false>(voxel);
+    float fa = a - floorf(a), fb = b - floorf(b);
+    float ts = (float)f.p.atlasTextureSize, as = (float)f.p.atlasSize;
+    *u = (fa + (float)m.tx) * ts / as;
+    *v = 1.0f - ((1.0f - fb) + (float)m.ty) * ts / as;
+  }
+
+  VRT_HD V3 normal_of(const Hit& h) const {
+    return mk3(h.axis == 0 ? h.nsign : 0.0f, h.axis == 1 ? h.nsign : 0.0f, h.axis == 2 ? h.nsign : 0.0f);
+  }
+
+  // GetReflectionRay (voxel.glsl:203-215)
+  VRT_HD Ray reflection_of(const Ray& r, const Hit& h) const {
+    V3 n = normal_of(h);
+    Ray o;
+    o.medium = 0;
+    o.pos = h.point;
+    o.dir = randomize_direction(reflect3(r.dir, n), h.point, f.p.reflectionNoise, f.p.time);
+    o.len = h.len;
+    o.energy = r.energy * (1.0f - dot3(mk3(-n.x, -n.y, -n.z), r.dir));
+    o.nrefl = r.nrefl + 1;
+    o.ntrans = r.ntrans;
+    o.face_axis = h.axis;
+    o.face_nsign = h.nsign;
+    return o;
+  }
+
+  // GetRefractionRay (voxel.glsl:217-246)
+  VRT_HD Ray refraction_of(const Ray& r, const Hit& h) const {
+    V3 n = normal_of(h);
+    float n_out = refractivity(voxel_at(h.point.x + n.x * 0.5f, h.point.y + n.y * 0.5f, h.point.z + n.z * 0.5f, nullptr));
+    float n_in = refractivity(voxel_at(h.point.x - n.x * 0.5f, h.point.y - n.y * 0.5f, h.point.z - n.z * 0.5f, nullptr));
+    V3 I = normalize3(r.dir);
+    float eta = n_out / n_in;
+    float d = dot3(n, I);
+    float k = 1.0f - eta * eta * (1.0f - d * d);
+    V3 t = mk3(0.0f, 0.0f, 0.0f);
+    if (!(k < 0.0f)) {
+      float s = eta * d + sqrtf(k);
+      t = mk3(eta * I.x - s * n.x, eta * I.y - s * n.y, eta * I.z - s * n.z);
+    }
+    Ray o;
+    if (t.x == 0.0f && t.y == 0.0f && t.z == 0.0f) {  // total internal reflection
+      o = reflection_of(r, h);
+      o.medium = r.medium;
+      o.energy = r.energy;
+    } else {
+      o.medium = h.voxel;
+      o.pos = h.point;
+      o.dir = randomize_direction(t, h.point, f.p.refractionNoise, f.p.time);
+      o.energy = r.energy;
+      if (r.medium == 0) {
+        float c[4];
+        color_of(h, c);
+        o.energy *= 1.0f - c[3];
+      }
+    }
+    o.len = h.len;
+    o.nrefl = r.nrefl;
+    o.ntrans = r.ntrans + 1;
+    o.face_axis = h.axis;
+    o.face_nsign = h.nsign;
+    return o;
+  }
+
+  // GetSkyboxColor (voxel.glsl:386-393) with pin G2
+  VRT_HD V3 sky(const Ray& r, V3 color) const {
+    V3 u = normalize3(r.dir);
+    float d = dot3(f.sun_unit, u);
+    float sun = d < 0.0f ? 0.0f : 10.0f * powf(d, 400.0f);
+    float grad = (u.y + 1.0f) * 0.5f;
+    V3 s = mk3(gmax(0.0f, sun) * f.day, gmax(grad * 0.75f, sun) * f.day, gmax(grad, 0.0f) * f.day);
+    return mix3(s, color, 1.0f - r.energy);
+  }
+};
+
+// TraceWithShadow (voxel.glsl:395-423)
+template <class Tracer, bool FLAT, bool COUNT>
+VRT_HD Hit trace_with_shadow(PixelCtx<FLAT, COUNT>& cx, Ray& r, V3& color) {
+  Hit h = Tracer::march(cx, r);
+  if (h.found) {
+    cx.count(CNT_HITS);
+    Ray s;
+    s.medium = h.voxel;
+    s.pos = h.point;
+    s.dir = cx.f.sun_unit;
+    s.len = h.len;
+    s.energy = r.energy;
+    s.nrefl = 0;
+    s.ntrans = 0;
+    s.face_axis = h.axis;
+    s.face_nsign = h.nsign;
+    bool shadowed = Tracer::shadow(cx, s, h);
+    float brightness = 0.3f;  // ambient (voxel.glsl:91)
+    if (!shadowed) {
+      MatProps m = material_of<FLAT>(h.voxel);
+      V3 n = cx.normal_of(h);
+      float diffuse = m.kd * gmax(dot3(n, s.dir), 0.0f);
+      float specular = m.ks * powf(gmax(dot3(reflect3(s.dir, n), r.dir), 0.0f), m.ke);
+      brightness = (0.3f + diffuse) + specular;
+    }
+    float c[4];
+    cx.color_of(h, c);
+    color = mix3(color, mk3((c[0] * c[3]) * brightness, (c[1] * c[3]) * brightness, (c[2] * c[3]) * brightness), r.energy);
+  } else {
+    color = mix3(cx.sky(r, color), color, 1.0f - r.energy);
+  }
+  return h;
+}
+
+struct PixelResult {
+  float rgba[4];
+  uint32_t hit;
+  int bounces;
+};
+
+// Vertex stage at the pixel centre (voxel.glsl:467-475) + fragment main (voxel.glsl:425-452)
+template <class Tracer, bool FLAT, bool COUNT>
+VRT_HD PixelResult shade_pixel(PixelCtx<FLAT, COUNT>& cx, int px, int py) {
+  const vrt_params& p = cx.f.p;
+  const float* m = p.invPV;
+  float nx = ((float)px + 0.5f) / (float)p.width * 2.0f - 1.0f;
+  float ny = ((float)py + 0.5f) / (float)p.height * 2.0f - 1.0f;
+  float nr[4], fr[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    float xy = m[i] * nx + m[4 + i] * ny;
+    nr[i] = (xy + m[8 + i] * -1.0f) + m[12 + i] * 1.0f;
+    fr[i] = (xy + m[8 + i] * 1.0f) + m[12 + i] * 1.0f;
+  }
+  V3 vnear = mk3(nr[0] / nr[3], nr[1] / nr[3], nr[2] / nr[3]);
+  V3 vdir = mk3(fr[0] / fr[3] - vnear.x, fr[1] / fr[3] - vnear.y, fr[2] / fr[3] - vnear.z);
+
+  constexpr int kStack = 8;  // maxReflections + maxTransparencies + 1 <= 8 (checked by the API)
+  Ray stack[kStack];
+  float half = cx.f.fsize * 0.5f;
+  Ray r0;
+  r0.pos = mk3(vnear.x + half, vnear.y + half, vnear.z + half);
+  r0.dir = randomize_direction(normalize3(vdir), vnear, p.rayNoise, p.time);
+  r0.len = 0.0f; r0.energy = 1.0f; r0.medium = 0; r0.nrefl = 0; r0.ntrans = 0; r0.face_axis = -1; r0.face_nsign = 0.0f;
+  stack[0] = r0;
+  int n = 1, popped = 0;
+  V3 color = mk3(0.0f, 0.0f, 0.0f);
+  PixelResult out;
+  out.hit = VRT_HIT_MISS;
+  while (n > 0) {
+    Ray r = stack[--n];
+    cx.count(popped == 0 ? CNT_PRIMARY : CNT_SECONDARY);
+    Hit h = trace_with_shadow<Tracer, FLAT, COUNT>(cx, r, color);
+    if (popped == 0 && h.found) out.hit = h.cell;
+    popped++;
+    if (h.found) {
+      MatProps mt = material_of<FLAT>(h.voxel);
+      if (mt.reflective && r.nrefl < p.maxReflections && n < kStack) stack[n++] = cx.reflection_of(r, h);
+      if (mt.transparent && r.ntrans < p.maxTransparencies) {
+        float c[4];
+        cx.color_of(h, c);
+        if (c[3] != 1.0f && n < kStack) stack[n++] = cx.refraction_of(r, h);
+      }
+    }
+  }
+  out.rgba[0] = color.x; out.rgba[1] = color.y; out.rgba[2] = color.z; out.rgba[3] = 1.0f;
+  out.bounces = popped;
+  return out;
+}
+
+}  // namespace vrt

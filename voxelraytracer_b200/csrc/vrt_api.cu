@@ -1,0 +1,441 @@
+// vrt_api.cu -- the extern "C" surface declared in include/vrt.h.
+// Owns the device copies of the reference's three GL objects (3D chunk texture, 2D atlas, FrameBuffer colour
+// attachment: src/main.cpp:160-320, src/FrameBuffer.cpp) and launches the kernels.  No CPU fallback exists:
+// without a CUDA device vrt_create() returns VRT_E_NO_DEVICE.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "vrt_internal.h"
+
+using namespace vrt;
+
+struct vrt_ctx {
+  int device = -1;
+  int num_sms = 0;
+  std::string err;
+  // chunk
+  int size = 0, log2n = 0;
+  uint8_t* d_grid = nullptr;       // n^3 raw bytes
+  uint16_t* d_cells = nullptr;     // (n+2)^3 traversal cells
+  // atlas
+  uint8_t* d_atlas = nullptr;
+  int atlasSize = 0, atlasTextureSize = 0;
+  // framebuffer + debug attachments (grown on demand)
+  uint8_t* d_fb = nullptr;  size_t fb_bytes = 0;
+  float* d_f32 = nullptr;   size_t f32_bytes = 0;
+  uint32_t* d_hit = nullptr; size_t hit_bytes = 0;
+  uint8_t* d_bounces = nullptr; size_t bounces_bytes = 0;
+  unsigned long long* d_counters = nullptr;  // CNT_N
+  unsigned long long* d_stats = nullptr;     // repack stats: [0] occupied voxels
+  int64_t last_pixels = 0;
+  cudaStream_t last_stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool timed = false;
+  int64_t launches = 0;
+  vrt_grid_info info{};
+};
+
+static thread_local std::string g_err = "";
+
+static int fail(vrt_ctx* c, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  if (c) c->err = buf;
+  return code;
+}
+#define CU(call)                                                                                        \
+  do {                                                                                                  \
+    cudaError_t e_ = (call);                                                                            \
+    if (e_ != cudaSuccess) return fail(ctx, e_ == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA,   \
+                                       "%s failed: %s", #call, cudaGetErrorString(e_));                 \
+  } while (0)
+
+static int bind(vrt_ctx* ctx) {
+  CU(cudaSetDevice(ctx->device));
+  return VRT_OK;
+}
+
+template <class T>
+static int ensure(vrt_ctx* ctx, T** p, size_t* have, size_t want) {
+  if (*have >= want && *p) return VRT_OK;
+  if (*p) { cudaFree(*p); *p = nullptr; *have = 0; }
+  CU(cudaMalloc((void**)p, want));
+  *have = want;
+  return VRT_OK;
+}
+
+extern "C" {
+
+const char* vrt_last_error(const vrt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_err.c_str(); }
+
+int vrt_create(int device, vrt_ctx** out) {
+  vrt_ctx* ctx = nullptr;
+  if (!out) return fail(nullptr, VRT_E_INVALID, "vrt_create: out is NULL");
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+    return fail(nullptr, VRT_E_NO_DEVICE, "vrt_create: no CUDA device (%s); this library has no CPU fallback",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  if (device < 0 || device >= count) return fail(nullptr, VRT_E_INVALID, "vrt_create: device %d out of range [0,%d)", device, count);
+  ctx = new (std::nothrow) vrt_ctx();
+  if (!ctx) return fail(nullptr, VRT_E_OOM, "vrt_create: out of host memory");
+  ctx->device = device;
+  cudaDeviceProp prop;
+  e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->d_counters, sizeof(unsigned long long) * (CNT_N + 8));
+  if (e == cudaSuccess) e = cudaMemset(ctx->d_counters, 0, sizeof(unsigned long long) * (CNT_N + 8));
+  if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
+  if (e != cudaSuccess) {
+    int code = fail(nullptr, VRT_E_CUDA, "vrt_create: %s", cudaGetErrorString(e));
+    delete ctx;
+    return code;
+  }
+  ctx->d_stats = ctx->d_counters + CNT_N;
+  ctx->num_sms = prop.multiProcessorCount;
+  *out = ctx;
+  return VRT_OK;
+}
+
+int vrt_destroy(vrt_ctx* ctx) {
+  if (!ctx) return VRT_OK;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  cudaFree(ctx->d_grid); cudaFree(ctx->d_cells); cudaFree(ctx->d_atlas); cudaFree(ctx->d_fb); cudaFree(ctx->d_f32);
+  cudaFree(ctx->d_hit); cudaFree(ctx->d_bounces); cudaFree(ctx->d_counters);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  delete ctx;
+  return VRT_OK;
+}
+
+static int repack_locked(vrt_ctx* ctx, int size, cudaStream_t s) {
+  const size_t n3 = (size_t)size * size * size, p3 = (size_t)(size + 2) * (size + 2) * (size + 2);
+  if (ctx->d_cells) { cudaFree(ctx->d_cells); ctx->d_cells = nullptr; }
+  CU(cudaMalloc((void**)&ctx->d_cells, p3 * sizeof(uint16_t)));
+  uint8_t *ta = nullptr, *tb = nullptr;
+  CU(cudaMalloc((void**)&ta, n3));
+  cudaError_t e = cudaMalloc((void**)&tb, n3);
+  if (e != cudaSuccess) { cudaFree(ta); return fail(ctx, VRT_E_OOM, "repack scratch: %s", cudaGetErrorString(e)); }
+  cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * 8, s);
+  int launches = 0;
+  // Radius cap: 255 fits the byte; for big chunks a smaller cap bounds the build time (O(radius) per voxel).
+  const int cap = size <= 256 ? 255 : 96;
+  e = launch_repack(ctx->d_grid, size, cap, ta, tb, ctx->d_cells, ctx->d_stats, s, &launches);
+  ctx->launches += launches;
+  cudaError_t e2 = cudaStreamSynchronize(s);
+  cudaFree(ta); cudaFree(tb);
+  if (e != cudaSuccess || e2 != cudaSuccess)
+    return fail(ctx, VRT_E_CUDA, "repack: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+  unsigned long long occ = 0;
+  CU(cudaMemcpy(&occ, ctx->d_stats, sizeof(occ), cudaMemcpyDeviceToHost));
+  ctx->size = size;
+  ctx->log2n = 0;
+  while ((1 << ctx->log2n) < size) ctx->log2n++;
+  ctx->info.size = size; ctx->info.pitch = size + 2; ctx->info.radius_cap = cap; ctx->info.reserved = 0;
+  ctx->info.cells_total = (int64_t)p3; ctx->info.voxels_occupied = (int64_t)occ;
+  return VRT_OK;
+}
+
+static int check_size(vrt_ctx* ctx, int size) {
+  if (size < 8 || size > 2048 || (size & (size - 1)) != 0)
+    return fail(ctx, VRT_E_INVALID, "grid size %d: must be a power of two in [8, 2048]", size);
+  return VRT_OK;
+}
+
+int vrt_upload_grid(vrt_ctx* ctx, const uint8_t* voxels, int size) {
+  if (!ctx || !voxels) return fail(ctx, VRT_E_INVALID, "vrt_upload_grid: NULL argument");
+  int rc = check_size(ctx, size);
+  if (rc) return rc;
+  if ((rc = bind(ctx))) return rc;
+  const size_t n3 = (size_t)size * size * size;
+  if (ctx->d_grid) { cudaFree(ctx->d_grid); ctx->d_grid = nullptr; ctx->size = 0; }
+  CU(cudaMalloc((void**)&ctx->d_grid, n3));
+  CU(cudaMemcpy(ctx->d_grid, voxels, n3, cudaMemcpyHostToDevice));
+  return repack_locked(ctx, size, nullptr);
+}
+
+int vrt_upload_grid_device(vrt_ctx* ctx, const void* d_voxels, int size, void* stream) {
+  if (!ctx || !d_voxels) return fail(ctx, VRT_E_INVALID, "vrt_upload_grid_device: NULL argument");
+  int rc = check_size(ctx, size);
+  if (rc) return rc;
+  if ((rc = bind(ctx))) return rc;
+  const size_t n3 = (size_t)size * size * size;
+  if (ctx->d_grid) { cudaFree(ctx->d_grid); ctx->d_grid = nullptr; ctx->size = 0; }
+  CU(cudaMalloc((void**)&ctx->d_grid, n3));
+  CU(cudaMemcpyAsync(ctx->d_grid, d_voxels, n3, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return repack_locked(ctx, size, (cudaStream_t)stream);
+}
+
+int vrt_upload_atlas(vrt_ctx* ctx, const uint8_t* rgba8, int atlasSize, int textureSize) {
+  if (!ctx || !rgba8) return fail(ctx, VRT_E_INVALID, "vrt_upload_atlas: NULL argument");
+  if (atlasSize < 1 || atlasSize > 16384 || textureSize < 1 || textureSize > atlasSize)
+    return fail(ctx, VRT_E_INVALID, "vrt_upload_atlas: atlasSize %d / textureSize %d", atlasSize, textureSize);
+  int rc = bind(ctx);
+  if (rc) return rc;
+  if (ctx->d_atlas) { cudaFree(ctx->d_atlas); ctx->d_atlas = nullptr; }
+  const size_t bytes = (size_t)atlasSize * atlasSize * 4;
+  CU(cudaMalloc((void**)&ctx->d_atlas, bytes));
+  CU(cudaMemcpy(ctx->d_atlas, rgba8, bytes, cudaMemcpyHostToDevice));
+  ctx->atlasSize = atlasSize; ctx->atlasTextureSize = textureSize;
+  return VRT_OK;
+}
+
+static int validate(vrt_ctx* ctx, const vrt_params* p) {
+  if (!ctx || !p) return fail(ctx, VRT_E_INVALID, "render: NULL argument");
+  if (!ctx->d_grid || !ctx->d_cells) return fail(ctx, VRT_E_NOT_READY, "render: no grid uploaded");
+  if (p->size != ctx->size) return fail(ctx, VRT_E_INVALID, "render: params.size %d != uploaded grid size %d", p->size, ctx->size);
+  if (p->width < 1 || p->height < 1 || p->width > 65536 || p->height > 65536) return fail(ctx, VRT_E_INVALID, "render: frame %dx%d", p->width, p->height);
+  if (p->tile_w < 1 || p->tile_h < 1 || p->tile_x0 < 0 || p->tile_y0 < 0 || p->tile_x0 + p->tile_w > p->width || p->tile_y0 + p->tile_h > p->height)
+    return fail(ctx, VRT_E_INVALID, "render: tile (%d,%d %dx%d) outside frame %dx%d", p->tile_x0, p->tile_y0, p->tile_w, p->tile_h, p->width, p->height);
+  if (p->band_count > 1 && (p->band_rows < 1 || p->band_index < 0 || p->band_index >= p->band_count))
+    return fail(ctx, VRT_E_INVALID, "render: band_rows %d band_count %d band_index %d", p->band_rows, p->band_count, p->band_index);
+  if (p->maxReflections < 0 || p->maxTransparencies < 0 || p->maxReflections + p->maxTransparencies > 7)
+    return fail(ctx, VRT_E_INVALID, "render: maxReflections %d + maxTransparencies %d must be in [0,7]", p->maxReflections, p->maxTransparencies);
+  if (!(p->flags & VRT_FLAG_COLOR_ONLY)) {
+    if (!ctx->d_atlas) return fail(ctx, VRT_E_NOT_READY, "render: textured shading needs an atlas (vrt_upload_atlas) or VRT_FLAG_COLOR_ONLY");
+    if (p->atlasSize != ctx->atlasSize || p->atlasTextureSize != ctx->atlasTextureSize)
+      return fail(ctx, VRT_E_INVALID, "render: params atlas %d/%d != uploaded atlas %d/%d", p->atlasSize, p->atlasTextureSize, ctx->atlasSize, ctx->atlasTextureSize);
+  }
+  return VRT_OK;
+}
+
+static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaStream_t s) {
+  int rc = validate(ctx, p);
+  if (rc) return rc;
+  if ((rc = bind(ctx))) return rc;
+  const int64_t npix = vrt_tile_pixels(p);
+  if (npix <= 0) return fail(ctx, VRT_E_INVALID, "render: empty tile");
+  const bool debug = (p->flags & (VRT_FLAG_DEBUG_MAPS | VRT_FLAG_COUNTERS | VRT_FLAG_FLOAT_OUT)) != 0;
+  FrameArgs a;
+  memset(&a, 0, sizeof(a));
+  a.p = *p;
+  a.grid = ctx->d_grid; a.cells = ctx->d_cells; a.atlas = ctx->d_atlas;
+  if (!d_out) {
+    if ((rc = ensure(ctx, &ctx->d_fb, &ctx->fb_bytes, (size_t)npix * 4))) return rc;
+    d_out = ctx->d_fb;
+  }
+  a.out_rgba8 = d_out;
+  if (p->flags & VRT_FLAG_FLOAT_OUT) {
+    if ((rc = ensure(ctx, &ctx->d_f32, &ctx->f32_bytes, (size_t)npix * 16))) return rc;
+    a.out_f32 = ctx->d_f32;
+  }
+  if (p->flags & VRT_FLAG_DEBUG_MAPS) {
+    if ((rc = ensure(ctx, &ctx->d_hit, &ctx->hit_bytes, (size_t)npix * 4))) return rc;
+    if ((rc = ensure(ctx, &ctx->d_bounces, &ctx->bounces_bytes, (size_t)npix))) return rc;
+    a.out_hit = ctx->d_hit; a.out_bounces = ctx->d_bounces;
+  }
+  if (p->flags & VRT_FLAG_COUNTERS) a.counters = ctx->d_counters;
+  a.sun_unit = normalize3(mk3(p->sunDir[0], p->sunDir[1], p->sunDir[2]));  // IEEE float ops, same bits as on the device
+  a.fsize = (float)p->size;
+  a.day = gmax(p->sunDir[1], 0.0f);
+  a.rows_local = (int)(npix / p->tile_w);
+  a.log2n = ctx->log2n;
+  CU(cudaEventRecord(ctx->ev0, s));
+  CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, s));
+  CU(cudaEventRecord(ctx->ev1, s));
+  ctx->launches += 1;
+  ctx->timed = true;
+  ctx->last_pixels = npix;
+  ctx->last_stream = s;
+  return VRT_OK;
+}
+
+int vrt_render(vrt_ctx* ctx, const vrt_params* p, void* stream) { return render_impl(ctx, p, nullptr, (cudaStream_t)stream); }
+
+int vrt_render_to(vrt_ctx* ctx, const vrt_params* p, void* d_rgba8, void* stream) {
+  if (!d_rgba8) return fail(ctx, VRT_E_INVALID, "vrt_render_to: NULL output");
+  return render_impl(ctx, p, (uint8_t*)d_rgba8, (cudaStream_t)stream);
+}
+
+int vrt_render_host(vrt_ctx* ctx, const vrt_params* p, uint8_t* host_rgba8, void* stream) {
+  if (!host_rgba8) return fail(ctx, VRT_E_INVALID, "vrt_render_host: NULL output");
+  int rc = render_impl(ctx, p, nullptr, (cudaStream_t)stream);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(host_rgba8, ctx->d_fb, (size_t)ctx->last_pixels * 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return VRT_OK;
+}
+
+int vrt_framebuffer_device(vrt_ctx* ctx, void** d_rgba8, size_t* bytes) {
+  if (!ctx || !d_rgba8) return fail(ctx, VRT_E_INVALID, "vrt_framebuffer_device: NULL argument");
+  *d_rgba8 = ctx->d_fb;
+  if (bytes) *bytes = (size_t)ctx->last_pixels * 4;
+  return ctx->d_fb ? VRT_OK : fail(ctx, VRT_E_NOT_READY, "vrt_framebuffer_device: nothing rendered yet");
+}
+
+int vrt_read_framebuffer(vrt_ctx* ctx, uint8_t* host, size_t bytes) {
+  if (!ctx || !host) return fail(ctx, VRT_E_INVALID, "vrt_read_framebuffer: NULL argument");
+  if (!ctx->d_fb || ctx->last_pixels == 0) return fail(ctx, VRT_E_NOT_READY, "vrt_read_framebuffer: nothing rendered yet");
+  if (bytes < (size_t)ctx->last_pixels * 4) return fail(ctx, VRT_E_INVALID, "vrt_read_framebuffer: buffer %zu < %zu bytes", bytes, (size_t)ctx->last_pixels * 4);
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(ctx->last_stream));
+  CU(cudaMemcpy(host, ctx->d_fb, (size_t)ctx->last_pixels * 4, cudaMemcpyDeviceToHost));
+  return VRT_OK;
+}
+
+int vrt_read_debug_maps(vrt_ctx* ctx, uint32_t* hit, uint8_t* bounces, size_t npix) {
+  if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_read_debug_maps: NULL ctx");
+  if (!ctx->d_hit || !ctx->d_bounces || npix > (size_t)ctx->last_pixels) return fail(ctx, VRT_E_NOT_READY, "vrt_read_debug_maps: no debug maps for %zu pixels", npix);
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(ctx->last_stream));
+  if (hit) CU(cudaMemcpy(hit, ctx->d_hit, npix * 4, cudaMemcpyDeviceToHost));
+  if (bounces) CU(cudaMemcpy(bounces, ctx->d_bounces, npix, cudaMemcpyDeviceToHost));
+  return VRT_OK;
+}
+
+int vrt_read_float_frame(vrt_ctx* ctx, float* rgba, size_t npix) {
+  if (!ctx || !rgba) return fail(ctx, VRT_E_INVALID, "vrt_read_float_frame: NULL argument");
+  if (!ctx->d_f32 || npix > (size_t)ctx->last_pixels) return fail(ctx, VRT_E_NOT_READY, "vrt_read_float_frame: no float frame for %zu pixels", npix);
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(ctx->last_stream));
+  CU(cudaMemcpy(rgba, ctx->d_f32, npix * 16, cudaMemcpyDeviceToHost));
+  return VRT_OK;
+}
+
+int vrt_reset_counters(vrt_ctx* ctx) {
+  if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_reset_counters: NULL ctx");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemset(ctx->d_counters, 0, sizeof(unsigned long long) * CNT_N));
+  return VRT_OK;
+}
+
+int vrt_get_counters(vrt_ctx* ctx, vrt_counters* out) {
+  if (!ctx || !out) return fail(ctx, VRT_E_INVALID, "vrt_get_counters: NULL argument");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  unsigned long long h[CNT_N];
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy(h, ctx->d_counters, sizeof(h), cudaMemcpyDeviceToHost));
+  out->primary_rays = h[CNT_PRIMARY]; out->secondary_rays = h[CNT_SECONDARY]; out->shadow_rays = h[CNT_SHADOW];
+  out->march_steps = h[CNT_MARCH_STEPS]; out->shadow_steps = h[CNT_SHADOW_STEPS]; out->actual_steps = h[CNT_ACTUAL_STEPS];
+  out->hits = h[CNT_HITS]; out->tie_index3 = h[CNT_TIE3];
+  return VRT_OK;
+}
+
+int vrt_last_render_ms(vrt_ctx* ctx, float* ms) {
+  if (!ctx || !ms) return fail(ctx, VRT_E_INVALID, "vrt_last_render_ms: NULL argument");
+  if (!ctx->timed) return fail(ctx, VRT_E_NOT_READY, "vrt_last_render_ms: nothing rendered yet");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaEventSynchronize(ctx->ev1));
+  CU(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+  return VRT_OK;
+}
+
+int64_t vrt_kernel_launches(const vrt_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int vrt_grid_info_get(vrt_ctx* ctx, vrt_grid_info* out) {
+  if (!ctx || !out) return fail(ctx, VRT_E_INVALID, "vrt_grid_info_get: NULL argument");
+  if (!ctx->d_cells) return fail(ctx, VRT_E_NOT_READY, "vrt_grid_info_get: no grid uploaded");
+  *out = ctx->info;
+  return VRT_OK;
+}
+
+int vrt_read_cells(vrt_ctx* ctx, uint16_t* host, size_t count) {
+  if (!ctx || !host) return fail(ctx, VRT_E_INVALID, "vrt_read_cells: NULL argument");
+  if (!ctx->d_cells) return fail(ctx, VRT_E_NOT_READY, "vrt_read_cells: no grid uploaded");
+  const size_t p3 = (size_t)(ctx->size + 2) * (ctx->size + 2) * (ctx->size + 2);
+  if (count != p3) return fail(ctx, VRT_E_INVALID, "vrt_read_cells: count %zu != (size+2)^3 = %zu", count, p3);
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaMemcpy(host, ctx->d_cells, p3 * sizeof(uint16_t), cudaMemcpyDeviceToHost));
+  return VRT_OK;
+}
+
+int vrt_temporal_blend(vrt_ctx* ctx, const void* d_new, void* d_acc, int64_t npix, float alpha, void* stream) {
+  if (!ctx || !d_new || !d_acc || npix < 0) return fail(ctx, VRT_E_INVALID, "vrt_temporal_blend: bad argument");
+  if (((uintptr_t)d_new | (uintptr_t)d_acc) & 15) return fail(ctx, VRT_E_INVALID, "vrt_temporal_blend: buffers must be 16-byte aligned");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(launch_temporal_blend((const uint8_t*)d_new, (uint8_t*)d_acc, npix, alpha, (cudaStream_t)stream));
+  ctx->launches += 1;
+  return VRT_OK;
+}
+
+int vrt_host_alloc(vrt_ctx* ctx, size_t bytes, void** out) {
+  if (!ctx || !out) return fail(ctx, VRT_E_INVALID, "vrt_host_alloc: NULL argument");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+  return VRT_OK;
+}
+
+int vrt_host_free(vrt_ctx* ctx, void* p) {
+  if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_host_free: NULL ctx");
+  if (p) CU(cudaFreeHost(p));
+  return VRT_OK;
+}
+
+int vrt_device_alloc(vrt_ctx* ctx, size_t bytes, void** out) {
+  if (!ctx || !out) return fail(ctx, VRT_E_INVALID, "vrt_device_alloc: NULL argument");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaMalloc(out, bytes));
+  return VRT_OK;
+}
+
+int vrt_device_free(vrt_ctx* ctx, void* p) {
+  if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_device_free: NULL ctx");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  if (p) CU(cudaFree(p));
+  return VRT_OK;
+}
+
+int vrt_synchronize(vrt_ctx* ctx, void* stream) {
+  if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_synchronize: NULL ctx");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return VRT_OK;
+}
+
+int vrt_ipc_alloc_frame(vrt_ctx* ctx, size_t bytes, void** d_ptr, uint8_t handle[VRT_IPC_HANDLE_BYTES]) {
+  if (!ctx || !d_ptr || !handle) return fail(ctx, VRT_E_INVALID, "vrt_ipc_alloc_frame: NULL argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) <= VRT_IPC_HANDLE_BYTES, "handle size");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaMalloc(d_ptr, bytes));
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, *d_ptr));
+  memset(handle, 0, VRT_IPC_HANDLE_BYTES);
+  memcpy(handle, &h, sizeof(h));
+  return VRT_OK;
+}
+
+int vrt_ipc_open(vrt_ctx* ctx, const uint8_t handle[VRT_IPC_HANDLE_BYTES], void** d_ptr) {
+  if (!ctx || !d_ptr || !handle) return fail(ctx, VRT_E_INVALID, "vrt_ipc_open: NULL argument");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  CU(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return VRT_OK;
+}
+
+int vrt_ipc_close(vrt_ctx* ctx, void* d_ptr) {
+  if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_ipc_close: NULL ctx");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  if (d_ptr) CU(cudaIpcCloseMemHandle(d_ptr));
+  return VRT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,24 @@
+// vrt_internal.h -- declarations shared by the CUDA translation units of libvrt.so (not installed).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_common.cuh"
+
+namespace vrt {
+
+// kernels.cu: launches the per-pixel kernel variant selected by (exact, flat, debug).
+// grid/block are chosen inside; returns the cudaError of the launch.
+cudaError_t launch_render(const FrameArgs& args, bool exact, bool flat, bool debug, cudaStream_t stream);
+// Persistent variant of the fast kernel: one CTA per SM slot pulling 8x4-pixel warp tiles from an atomic queue.
+cudaError_t launch_render_persistent(const FrameArgs& args, bool flat, unsigned int* tile_counter, int num_sms, cudaStream_t stream);
+
+// repack.cu: raw R8 grid (n^3) -> padded uint16 cells ((n+2)^3), see rt_trace_fast.cuh.
+// tmp_a / tmp_b: n^3 bytes of scratch each.  Returns the number of kernels launched through *launches.
+cudaError_t launch_repack(const uint8_t* d_grid, int n, int radius_cap, uint8_t* tmp_a, uint8_t* tmp_b, uint16_t* d_cells,
+                          unsigned long long* d_stats, cudaStream_t stream, int* launches);
+
+// temporal.cu
+cudaError_t launch_temporal_blend(const uint8_t* d_new, uint8_t* d_acc, int64_t npix, float alpha, cudaStream_t stream);
+
+}  // namespace vrt
