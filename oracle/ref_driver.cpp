@@ -118,7 +118,7 @@ int vref_render(const vrt_params* p, const uint8_t* grid, const uint8_t* atlas, 
   set_uniforms(p, grid, atlas);
   if (nthreads < 1) nthreads = 1;
   std::atomic<int> next(0);
-  const int chunk = 4;
+  const int chunk = 1;
   auto work = [&]() {
     for (;;) {
       int r0 = next.fetch_add(chunk);

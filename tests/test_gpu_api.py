@@ -1,0 +1,96 @@
+"""C-ABI behaviour on the GPU: error codes, external output buffers, host round trip, temporal pass, timing."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import voxelraytracer_b200 as vrt
+from common import gpu_render, make_params, scene
+
+pytestmark = pytest.mark.gpu
+
+
+def test_errors_are_codes_not_aborts():
+    c = vrt.Context(0)
+    p = vrt.default_params(64, 64, 32)
+    with pytest.raises(vrt.VrtError) as e:
+        c.render(p)
+    assert e.value.code == -4                                   # VRT_E_NOT_READY: no grid
+    with pytest.raises(vrt.VrtError) as e:
+        c.upload_grid(np.zeros(24 ** 3, np.uint8), 24)
+    assert e.value.code == -1                                   # size must be a power of two
+    grid, n, atlas, ts = scene("glass_cube32")
+    c.upload_grid(grid, n)
+    with pytest.raises(vrt.VrtError) as e:
+        c.render(p)                                             # textured without an atlas
+    assert e.value.code == -4
+    p.flags = vrt.FLAG_COLOR_ONLY
+    c.render(p)
+    p.tile_w = 65
+    with pytest.raises(vrt.VrtError) as e:
+        c.render(p)
+    assert e.value.code == -1
+    p.tile_w = 64; p.size = 64
+    with pytest.raises(vrt.VrtError):
+        c.render(p)
+    p.size = 32; p.maxReflections = 9
+    with pytest.raises(vrt.VrtError):
+        c.render(p)
+    with pytest.raises(vrt.VrtError):
+        vrt.Context(4096)
+    c.close()
+
+
+def test_render_to_torch_tensor_and_render_host(ctx):
+    import torch
+    grid, n, atlas, ts = scene("terrain32")
+    ctx.upload_grid(grid, n); ctx.upload_atlas(atlas, ts)
+    W, H = 320, 200
+    p = make_params(W, H, "terrain32", "terrain32_above")
+    ref = gpu_render(ctx, p, flags_extra=0).rgba8
+    t = torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda:0")
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        ctx.render_to(p, t.data_ptr(), s.cuda_stream)
+    s.synchronize()
+    assert np.array_equal(t.cpu().numpy().reshape(-1, 4), ref)
+    host, hp = ctx.host_alloc(W * H * 4)
+    ctx.render_host(p, hp)
+    assert np.array_equal(host.reshape(-1, 4), ref)
+    assert ctx.last_render_ms() > 0.0
+    before = ctx.kernel_launches()
+    ctx.render(p); ctx.synchronize()
+    assert ctx.kernel_launches() == before + 1
+
+
+def test_temporal_blend_matches_formula(ctx):
+    import torch
+    rng = np.random.default_rng(0)
+    n = 1920 * 1080 + 3
+    a = rng.integers(0, 256, (n, 4), dtype=np.uint8)
+    b = rng.integers(0, 256, (n, 4), dtype=np.uint8)
+    ta, tb = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    for alpha in (1.0, 0.25):                                  # alpha = 1 is the reference default (main.cpp:155)
+        acc = tb.clone()
+        ctx.temporal_blend(ta.data_ptr(), acc.data_ptr(), n, alpha)
+        ctx.synchronize()
+        got = acc.cpu().numpy()
+        al = np.float32(alpha)
+        v = al * (a.astype(np.float32) / np.float32(255)) + (np.float32(1) - al) * (b.astype(np.float32) / np.float32(255))  # temporal.glsl:18
+        exp = np.floor(np.clip(v, 0, 1) * np.float32(255) + np.float32(0.5)).astype(np.uint8)
+        assert np.array_equal(got, exp)
+    assert np.array_equal(got if alpha == 1.0 else a, a)
+
+
+def test_two_contexts_are_independent():
+    c1, c2 = vrt.Context(0), vrt.Context(0)
+    g1, n1, a1, t1 = scene("glass_cube32")
+    g2, n2, a2, t2 = scene("refraction32")
+    c1.upload_grid(g1, n1); c2.upload_grid(g2, n2)
+    p1 = make_params(128, 128, "glass_cube32", "start", vrt.FLAG_COLOR_ONLY)
+    p2 = make_params(128, 128, "refraction32", "start", vrt.FLAG_COLOR_ONLY)
+    f1 = gpu_render(c1, p1, flags_extra=0).rgba8
+    f2 = gpu_render(c2, p2, flags_extra=0).rgba8
+    assert not np.array_equal(f1, f2)
+    assert np.array_equal(gpu_render(c1, p1, flags_extra=0).rgba8, f1)
+    c1.close(); c2.close()

@@ -1,0 +1,88 @@
+"""The product's device headers compiled for the host (tests/hostsim) against the oracle.
+Exact tracer: bit-identical.  Fast tracer: north_star's caps (hit map / bounce count differ on at most
+0.01 % of the frame; colour within 1/255 RMS per channel) - with a margin, at a size the CPU does in seconds."""
+import numpy as np
+import pytest
+
+import voxelraytracer_b200 as vrt
+from common import hostsim_cells, hostsim_render, make_params, oracle_render, rms255, scene
+
+CASES = [
+    ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY),
+    ("glass_cube32", "start", 0),
+    ("terrain32", "terrain32_above", 0),
+    ("terrain128", "terrain_inside", 0),
+    ("terrain128", "terrain_low", 0),
+    ("terrain128", "terrain_above", 0),
+    ("terrain128", "terrain_outside", 0),
+    ("terrain128_glass", "glass_wall", 0),
+    ("refraction128", "refraction_close", 0),
+    ("refraction128", "refraction_close", vrt.FLAG_COLOR_ONLY),
+]
+W, H = 480, 270
+
+
+@pytest.mark.parametrize("sc,pose,flags", CASES)
+def test_exact_tracer_is_bit_identical(sc, pose, flags):
+    grid, n, atlas, ts = scene(sc)
+    p = make_params(W, H, sc, pose, flags)
+    o = oracle_render(p, grid, atlas)
+    e = hostsim_render(p, grid, atlas, 0)
+    assert np.array_equal(e.hit, o.hit) and np.array_equal(e.bounces, o.bounces)
+    assert np.array_equal(e.f32.view(np.uint32), o.f32.view(np.uint32))
+    for k in ("primary_rays", "secondary_rays", "shadow_rays", "march_steps", "shadow_steps", "hits", "tie_index3"):
+        assert e.counters[k] == o.counters[k], k
+
+
+def test_exact_tracer_with_noise_is_bit_identical():
+    grid, n, atlas, ts = scene("glass_cube32")
+    p = make_params(200, 200, "glass_cube32", "start", vrt.FLAG_COLOR_ONLY, noise=(0.02, 0.1, 0.1), time=7.0)
+    o = oracle_render(p, grid, atlas)
+    e = hostsim_render(p, grid, atlas, 0)
+    assert np.array_equal(e.f32.view(np.uint32), o.f32.view(np.uint32)) and np.array_equal(e.bounces, o.bounces)
+
+
+@pytest.mark.parametrize("sc,pose,flags", CASES)
+def test_fast_tracer_within_caps(sc, pose, flags):
+    grid, n, atlas, ts = scene(sc)
+    p = make_params(W, H, sc, pose, flags)
+    o = oracle_render(p, grid, atlas)
+    f = hostsim_render(p, grid, atlas, 1)
+    npx = len(o.hit)
+    bad = int(((f.hit != o.hit) | (f.bounces != o.bounces)).sum())
+    assert bad <= max(2, int(1e-4 * npx)), "hit/bounce mismatches: %d of %d" % (bad, npx)   # 0.01 % (floor 2 px at this size)
+    r = rms255(f.rgba8, o.rgba8)
+    assert (r <= 1.0).all(), r
+    # the walk looks at far fewer cells than the shader steps through
+    s_ref = o.counters["march_steps"] + o.counters["shadow_steps"]
+    assert f.counters["actual_steps"] < s_ref
+    assert f.counters["primary_rays"] == o.counters["primary_rays"]
+
+
+def test_fast_tracer_custom_limits_and_ray_length():
+    grid, n, atlas, ts = scene("glass_cube32")
+    p = make_params(320, 180, "glass_cube32", "start")
+    p.maxReflections, p.maxTransparencies, p.maxRayLength = 2, 3, 60.0
+    o = oracle_render(p, grid, atlas)
+    f = hostsim_render(p, grid, atlas, 1)
+    bad = int(((f.hit != o.hit) | (f.bounces != o.bounces)).sum())
+    assert bad <= 3 and o.bounces.max() > 4, o.bounces.max()  # default limits give at most 4 here
+    assert (rms255(f.rgba8, o.rgba8) <= 1.0).all()
+
+
+def test_cells_radius_is_exact_chebyshev_distance():
+    rng = np.random.default_rng(3)
+    n = 16
+    g = (rng.random(n ** 3) < 0.01).astype(np.uint8) * rng.integers(1, 4, n ** 3).astype(np.uint8)
+    cells = hostsim_cells(g, n).reshape(n + 2, n + 2, n + 2)
+    occ = np.ones((n + 2,) * 3, bool)          # border counts as an obstacle
+    occ[1:-1, 1:-1, 1:-1] = g.reshape(n, n, n) != 0
+    zz, yy, xx = np.nonzero(occ)
+    pts = np.stack([zz, yy, xx], 1)
+    for _ in range(300):
+        c = rng.integers(1, n + 1, 3)
+        d = np.abs(pts - c).max(axis=1).min()
+        v = int(cells[c[0], c[1], c[2]])
+        assert (v >> 8) == min(d, 255)
+        assert (v & 0xFF) == g.reshape(n, n, n)[c[0] - 1, c[1] - 1, c[2] - 1]
+    assert (cells[0] == 0).all() and (cells[:, 0] == 0).all() and (cells[:, :, -1] == 0).all()
