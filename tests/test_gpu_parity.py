@@ -145,4 +145,4 @@ def test_synthetic_256_and_long_rays(ctx):
     bad = int(((g.hit != o.hit) | (g.bounces != o.bounces)).sum())
     assert bad <= max(2, int(1e-4 * 640 * 360)), bad
     assert (rms255(g.rgba8, o.rgba8) <= 1.0).all()
-    assert (o.hit != vrt.HIT_MISS).mean() > 0.2
+    assert (o.hit != vrt.HIT_MISS).mean() > 0.1

@@ -44,30 +44,38 @@ struct FastTracer {
   typedef PixelCtx<FLAT, COUNT> Ctx;
 
   struct Walk {
-    V3 o, d, inv;          // origin, direction, 1/direction (inf where d == 0)
-    V3 tmax, tdel;         // next plane crossing time per axis / time per cell
-    V3 off;                // 1 where d > 0 else 0: next plane of cell c is c + off
+    V3 o, d, inv;          // origin, direction, 1/direction (+inf where d == 0)
+    V3 tmax, tdel;         // next plane crossing time per axis / time per cell (0 where d == 0)
+    V3 off;                // 1 where d >= 0 else 0: the next plane of cell c is c + off
     float invmax;          // 1 / max |d|
+    float jbias;           // (1 + 1/64) * invmax: a jump advances by r * invmax - jbias
     int dix, diy, diz;     // padded-index increment per axis step
     uint32_t idx;          // padded index of the current cell
+    uint32_t ibias;        // constant folded into the jump's index computation (device path)
     float t, tprev;        // entry time of the current cell / of its predecessor
-    int axis;              // axis of the last plane crossed
+    bool sx, sy;           // last plane crossed: x / y / (neither) z
     bool zx, zy, zz;       // d == 0 per axis
   };
 
   static VRT_HD float finf() { return u2f(0x7F800000u); }
+  static VRT_HD int last_axis(const Walk& w) { return w.sx ? 0 : (w.sy ? 1 : 2); }
 
   // Sets the direction-dependent constants.
   static VRT_HD void set_dir(Walk& w, const V3& o, const V3& d, int P) {
     w.o = o; w.d = d;
     w.zx = d.x == 0.0f; w.zy = d.y == 0.0f; w.zz = d.z == 0.0f;
-    w.inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    // For a zero component: inv = +inf and off = 1, so (floor(o) + 1 - o) * inv = +inf, never NaN, never the minimum.
+    w.inv = mk3(w.zx ? finf() : 1.0f / d.x, w.zy ? finf() : 1.0f / d.y, w.zz ? finf() : 1.0f / d.z);
     w.tdel = mk3(w.zx ? 0.0f : fabsf(w.inv.x), w.zy ? 0.0f : fabsf(w.inv.y), w.zz ? 0.0f : fabsf(w.inv.z));
-    w.off = mk3(d.x > 0.0f ? 1.0f : 0.0f, d.y > 0.0f ? 1.0f : 0.0f, d.z > 0.0f ? 1.0f : 0.0f);
+    w.off = mk3(d.x >= 0.0f ? 1.0f : 0.0f, d.y >= 0.0f ? 1.0f : 0.0f, d.z >= 0.0f ? 1.0f : 0.0f);
     w.invmax = 1.0f / fmaxf(fabsf(d.x), fmaxf(fabsf(d.y), fabsf(d.z)));
+    w.jbias = 1.015625f * w.invmax;
     w.dix = d.x > 0.0f ? 1 : -1;
     w.diy = d.y > 0.0f ? P : -P;
     w.diz = d.z > 0.0f ? P * P : -(P * P);
+    // float->int by magic number: bits(q + 1.5*2^23, rounded down) = 0x4B400000 + floor(q); fold "+1" per axis too
+    w.ibias = (uint32_t)(0x4B400000u - 1u) * (uint32_t)(P * P + P + 1);
+    w.sx = false; w.sy = false;
   }
 
   // Places the walk in cell (cx,cy,cz) (unpadded integer coordinates, -1..n allowed) and derives the plane
@@ -81,28 +89,37 @@ struct FastTracer {
 
   // One Amanatides-Woo step: cross the nearest plane (ties: x before y before z).
   static VRT_HD void step(Walk& w) {
-    bool sx = w.tmax.x <= w.tmax.y && w.tmax.x <= w.tmax.z;
-    bool sy = !sx && w.tmax.y <= w.tmax.z;
+    const float m = fminf(w.tmax.x, fminf(w.tmax.y, w.tmax.z));
+    const bool sx = w.tmax.x == m;
+    const bool sy = !sx && w.tmax.y == m;
     w.tprev = w.t;
-    w.t = sx ? w.tmax.x : (sy ? w.tmax.y : w.tmax.z);
-    w.idx += (uint32_t)(sx ? w.dix : (sy ? w.diy : w.diz));
-    w.axis = sx ? 0 : (sy ? 1 : 2);
-    w.tmax.x += sx ? w.tdel.x : 0.0f;
-    w.tmax.y += sy ? w.tdel.y : 0.0f;
-    w.tmax.z += (!sx && !sy) ? w.tdel.z : 0.0f;
+    w.t = m;
+    if (sx) { w.idx += (uint32_t)w.dix; w.tmax.x += w.tdel.x; }
+    else if (sy) { w.idx += (uint32_t)w.diy; w.tmax.y += w.tdel.y; }
+    else { w.idx += (uint32_t)w.diz; w.tmax.z += w.tdel.z; }
+    w.sx = sx; w.sy = sy;
   }
 
-  // Jump inside the empty cube promised by radius r (r >= 2); returns false if the length cap forbids it.
+  // Jump inside the empty cube promised by radius r (r >= 2): advance by (r - 1 - 1/64) cells of dominant-axis
+  // travel, then re-derive the cell and the plane times from the position.  False if the length cap forbids it.
   static VRT_HD bool jump(Walk& w, uint32_t r, float tcap, int P) {
-    float adv = ((float)(r - 1u) - 0.015625f) * w.invmax;
-    float tn = w.t + adv;
+    // (float)r without a conversion instruction: 2^23 + r has r in its low mantissa bits
+    const float rf = u2f(0x4B000000u | r) - 8388608.0f;
+    const float tn = fmaf(rf, w.invmax, w.t - w.jbias);
     if (!(tn < tcap)) return false;
-    float qx = w.o.x + tn * w.d.x, qy = w.o.y + tn * w.d.y, qz = w.o.z + tn * w.d.z;
-    float fx = floorf(qx), fy = floorf(qy), fz = floorf(qz);
+    const float qx = fmaf(tn, w.d.x, w.o.x), qy = fmaf(tn, w.d.y, w.o.y), qz = fmaf(tn, w.d.z, w.o.z);
+#if defined(__CUDA_ARCH__)
+    // floor + float->int on the FMA/ALU pipes: add 1.5*2^23 rounding DOWN; the sum's low bits are floor(q)
+    const float mx = __fadd_rd(qx, 12582912.0f), my = __fadd_rd(qy, 12582912.0f), mz = __fadd_rd(qz, 12582912.0f);
+    const float fx = mx - 12582912.0f, fy = my - 12582912.0f, fz = mz - 12582912.0f;
+    w.idx = (f2u(mz) * (uint32_t)P + f2u(my)) * (uint32_t)P + f2u(mx) - w.ibias;
+#else
+    const float fx = floorf(qx), fy = floorf(qy), fz = floorf(qz);
     w.idx = (uint32_t)(((int)fz + 1) * P + ((int)fy + 1)) * (uint32_t)P + (uint32_t)((int)fx + 1);
-    w.tmax.x = w.zx ? finf() : ((fx + w.off.x) - w.o.x) * w.inv.x;
-    w.tmax.y = w.zy ? finf() : ((fy + w.off.y) - w.o.y) * w.inv.y;
-    w.tmax.z = w.zz ? finf() : ((fz + w.off.z) - w.o.z) * w.inv.z;
+#endif
+    w.tmax.x = ((fx + w.off.x) - w.o.x) * w.inv.x;
+    w.tmax.y = ((fy + w.off.y) - w.o.y) * w.inv.y;
+    w.tmax.z = ((fz + w.off.z) - w.o.z) * w.inv.z;
     w.tprev = w.t;
     w.t = tn;
     return true;
@@ -118,7 +135,6 @@ struct FastTracer {
   // Start of a ray.  Returns false when the ray can never touch the chunk.
   static VRT_HD bool begin(Walk& w, const Ray& r, float fsize, int n, int P) {
     set_dir(w, r.pos, r.dir, P);
-    w.axis = 0;
     const float fn1 = (float)(n - 1);
     if (r.face_axis >= 0) {
       // Spawned on a voxel face: the start cell is the one on the parent ray's side of the face, taken from
@@ -232,8 +248,8 @@ struct FastTracer {
       h.voxel = b;
       h.point = mk3(r.pos.x + w.t * r.dir.x, r.pos.y + w.t * r.dir.y, r.pos.z + w.t * r.dir.z);
       h.len = r.len + w.t;
-      h.axis = w.axis;
-      h.nsign = -sign1(vget(r.dir, w.axis));
+      h.axis = last_axis(w);
+      h.nsign = -sign1(vget(r.dir, h.axis));
       cx.tex_coord(h.point, h.axis, b, &h.u, &h.v);
       if (is_hit) {
         h.cell = unpadded_index(w.idx, P, cx.f.log2n);
