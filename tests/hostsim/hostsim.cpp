@@ -76,8 +76,8 @@ static void render_rows(const FrameArgs& f, std::atomic<int>& next, float* out_f
     if (ly >= f.rows_local) break;
     int py = frame_row(f.p, ly);
     for (int lx = 0; lx < f.p.tile_w; lx++) {
-      PixelCtx<FLAT, true> cx(f);
-      PixelResult r = shade_pixel<Tracer, FLAT, true>(cx, f.p.tile_x0 + lx, py);
+      typename Tracer::Ctx cx(f);
+      PixelResult r = shade_pixel<Tracer, FLAT>(cx, f.p.tile_x0 + lx, py);
       size_t o = (size_t)ly * f.p.tile_w + lx;
       if (out_f32) std::memcpy(out_f32 + o * 4, r.rgba, 16);
       if (out_rgba8) {
@@ -106,13 +106,8 @@ int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cel
   std::memset(&f, 0, sizeof(f));
   f.p = *p;
   f.grid = grid; f.cells = cells; f.atlas = atlas;
-  f.sun_unit = normalize3(mk3(p->sunDir[0], p->sunDir[1], p->sunDir[2]));
-  f.fsize = (float)p->size;
-  f.day = gmax(p->sunDir[1], 0.0f);
-  f.log2n = 0;
-  while ((1 << f.log2n) < p->size) f.log2n++;
-  if ((1 << f.log2n) != p->size) return -1;
   f.rows_local = (int)(vrt_tile_pixels(p) / p->tile_w);
+  if (!finish_frame_args(f)) return -1;
   bool flat = (p->flags & VRT_FLAG_COLOR_ONLY) != 0;
   uint64_t cnt[CNT_N] = {0};
   std::atomic<int> next(0);

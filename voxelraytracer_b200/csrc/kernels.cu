@@ -16,11 +16,11 @@ constexpr int kThreads = 32 * kCtaWarpsX * kCtaWarpsY;
 
 template <class Tracer, bool FLAT, bool DEBUG>
 __device__ __forceinline__ void render_one(const FrameArgs& f, int lx, int ly) {
-  PixelCtx<FLAT, DEBUG> cx(f);
+  typename Tracer::Ctx cx(f);
   const bool live = lx < f.p.tile_w && ly < f.rows_local;
   if (live) {
     const int px = f.p.tile_x0 + lx, py = frame_row(f.p, ly);
-    PixelResult r = shade_pixel<Tracer, FLAT, DEBUG>(cx, px, py);
+    PixelResult r = shade_pixel<Tracer, FLAT>(cx, px, py);
     const size_t o = (size_t)ly * (size_t)f.p.tile_w + (size_t)lx;
     uchar4 q;
     q.x = quantize_unorm8(r.rgba[0]); q.y = quantize_unorm8(r.rgba[1]); q.z = quantize_unorm8(r.rgba[2]); q.w = 255;

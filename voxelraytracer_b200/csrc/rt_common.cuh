@@ -70,6 +70,14 @@ VRT_HD V3 randomize_direction(V3 dir, V3 pos, float randomness, float seed) {
   float rz = random01(vx, vy, vz, 1.0f + seed);
   return normalize3(mk3(dir.x + (rx - 0.5f) * randomness, dir.y + (ry - 0.5f) * randomness, dir.z + (rz - 0.5f) * randomness));
 }
+// Same, for the fast traversal: with randomness == 0 (the reference's default, main.cpp:156-158) every offset is
+// (rnd - 0.5) * 0 = +-0 and dir + +-0 == dir, so the three hashes are skipped.  The only bit that can differ from the
+// literal form is the sign of a zero component, which the fast traversal never looks at (the exact one does, so it
+// keeps the literal form).
+VRT_HD V3 randomize_direction_lean(V3 dir, V3 pos, float randomness, float seed) {
+  if (randomness == 0.0f) return normalize3(mk3(dir.x + 0.0f, dir.y + 0.0f, dir.z + 0.0f));
+  return randomize_direction(dir, pos, randomness, seed);
+}
 
 // voxel.glsl:50-89 -- the two material tables, as functions of the clamped material index min(byte, 3)
 struct MatProps { float refr, kd, ks, ke; int tx, ty; bool transparent, reflective; };
@@ -129,6 +137,37 @@ struct Hit {
   uint32_t cell;       // x + y*n + z*n*n
 };
 
+// Direction-dependent constants of a grid walk (rt_trace_fast.cuh).
+struct DirConst {
+  V3 d, inv;             // direction, 1/direction (+inf where d == 0)
+  V3 tdel;               // time per cell (0 where d == 0)
+  V3 off;                // 1 where d >= 0 else 0: the next plane of cell c is c + off
+  float invmax;          // 1 / max |d|
+  float jbias;           // (1 + 1/64) * invmax: a jump advances by r * invmax - jbias
+  int dix, diy, diz;     // padded-index increment per axis step
+  uint32_t ibias;        // constant folded into the jump's index computation (device path)
+};
+
+VRT_HD float finf() { return u2f(0x7F800000u); }
+
+// Sets the direction-dependent constants of a walk (DirConst lives in rt_common.cuh because FrameArgs carries
+// one for the sun direction: every shadow ray of a frame shares it, so the host computes it once per frame).
+VRT_HD void set_dir_const(DirConst& w, const V3& d, int P) {
+  w.d = d;
+  const bool zx = d.x == 0.0f, zy = d.y == 0.0f, zz = d.z == 0.0f;
+  // For a zero component: inv = +inf and off = 1, so (floor(o) + 1 - o) * inv = +inf, never NaN, never the minimum.
+  w.inv = mk3(zx ? finf() : 1.0f / d.x, zy ? finf() : 1.0f / d.y, zz ? finf() : 1.0f / d.z);
+  w.tdel = mk3(zx ? 0.0f : fabsf(w.inv.x), zy ? 0.0f : fabsf(w.inv.y), zz ? 0.0f : fabsf(w.inv.z));
+  w.off = mk3(d.x >= 0.0f ? 1.0f : 0.0f, d.y >= 0.0f ? 1.0f : 0.0f, d.z >= 0.0f ? 1.0f : 0.0f);
+  w.invmax = 1.0f / fmaxf(fabsf(d.x), fmaxf(fabsf(d.y), fabsf(d.z)));
+  w.jbias = 1.015625f * w.invmax;
+  w.dix = d.x > 0.0f ? 1 : -1;
+  w.diy = d.y > 0.0f ? P : -P;
+  w.diz = d.z > 0.0f ? P * P : -(P * P);
+  // float->int by magic number: bits(q + 1.5*2^23, rounded down) = 0x4B400000 + floor(q); fold "+1" per axis too
+  w.ibias = (uint32_t)(0x4B400000u - 1u) * (uint32_t)(P * P + P + 1);
+}
+
 // Everything a pixel needs, passed by value as a __grid_constant__ kernel parameter.
 struct FrameArgs {
   vrt_params p;
@@ -141,11 +180,24 @@ struct FrameArgs {
   uint8_t* out_bounces;
   unsigned long long* counters;  // optional vrt_counters image (8 x u64)
   V3 sun_unit;              // normalize(u_SunDir)
+  DirConst sun;             // walk constants of sun_unit for this chunk (every shadow ray shares them)
   float fsize;              // (float)u_Size
   float day;                // max(u_SunDir.y, 0)
   int rows_local;           // number of compact rows this launch writes
   int log2n;
 };
+
+// Derived per-frame fields (host side, IEEE float ops: same bits as the device would compute).  p, the pointers
+// and rows_local must be set by the caller.  Returns false if p.size is not a power of two.
+inline bool finish_frame_args(FrameArgs& a) {
+  a.sun_unit = normalize3(mk3(a.p.sunDir[0], a.p.sunDir[1], a.p.sunDir[2]));
+  a.fsize = (float)a.p.size;
+  a.day = gmax(a.p.sunDir[1], 0.0f);
+  a.log2n = 0;
+  while ((1 << a.log2n) < a.p.size) a.log2n++;
+  set_dir_const(a.sun, a.sun_unit, a.p.size + 2);
+  return (1 << a.log2n) == a.p.size;
+}
 
 // local row -> frame row (band interleave, see include/vrt.h)
 VRT_HD int frame_row(const vrt_params& p, int ly) {

@@ -7,12 +7,26 @@
 
 namespace vrt {
 
-template <bool FLAT, bool COUNT>
+// LEAN selects the liberties only the fast traversal takes (hash skipped at zero noise, pow through ex2/lg2);
+// the exact traversal instantiates LEAN = false and stays a literal replay.
+template <bool FLAT, bool COUNT, bool LEAN = false>
 struct PixelCtx {
   const FrameArgs& f;
   PixelCounters cnt;
   VRT_HD explicit PixelCtx(const FrameArgs& fa) : f(fa) { if (COUNT) cnt.clear(); }
   VRT_HD void count(int which, uint32_t n = 1) { if (COUNT) cnt.v[which] += n; }
+
+  VRT_HD V3 jitter(V3 dir, V3 pos, float randomness) const {
+    return LEAN ? randomize_direction_lean(dir, pos, randomness, f.p.time) : randomize_direction(dir, pos, randomness, f.p.time);
+  }
+  // pow(x, e) for x >= 0, e > 0.  LEAN on the device: ex2(e * lg2(x)) on the SFU (relative error ~ e * 2^-22, far
+  // below the 1/255 colour bar); otherwise libm powf.
+  VRT_HD float pow_pos(float x, float e) const {
+#if defined(__CUDA_ARCH__)
+    if (LEAN) return x > 0.0f ? exp2f(e * __log2f(x)) : 0.0f;
+#endif
+    return powf(x, e);
+  }
 
   // GetVoxel (voxel.glsl:149-154) with REPEAT/NEAREST texel selection (G4).  u_Size is a power of two, so
   // coord/size*size == coord exactly and floor(coord) & (n-1) is the wrapped texel.
@@ -69,7 +83,7 @@ struct PixelCtx {
     Ray o;
     o.medium = 0;
     o.pos = h.point;
-    o.dir = randomize_direction(reflect3(r.dir, n), h.point, f.p.reflectionNoise, f.p.time);
+    o.dir = jitter(reflect3(r.dir, n), h.point, f.p.reflectionNoise);
     o.len = h.len;
     o.energy = r.energy * (1.0f - dot3(mk3(-n.x, -n.y, -n.z), r.dir));
     o.nrefl = r.nrefl + 1;
@@ -101,7 +115,7 @@ struct PixelCtx {
     } else {
       o.medium = h.voxel;
       o.pos = h.point;
-      o.dir = randomize_direction(t, h.point, f.p.refractionNoise, f.p.time);
+      o.dir = jitter(t, h.point, f.p.refractionNoise);
       o.energy = r.energy;
       if (r.medium == 0) {
         float c[4];
@@ -121,7 +135,7 @@ struct PixelCtx {
   VRT_HD V3 sky(const Ray& r, V3 color) const {
     V3 u = normalize3(r.dir);
     float d = dot3(f.sun_unit, u);
-    float sun = d < 0.0f ? 0.0f : 10.0f * powf(d, 400.0f);
+    float sun = d < 0.0f ? 0.0f : 10.0f * pow_pos(d, 400.0f);
     float grad = (u.y + 1.0f) * 0.5f;
     V3 s = mk3(gmax(0.0f, sun) * f.day, gmax(grad * 0.75f, sun) * f.day, gmax(grad, 0.0f) * f.day);
     return mix3(s, color, 1.0f - r.energy);
@@ -129,8 +143,8 @@ struct PixelCtx {
 };
 
 // TraceWithShadow (voxel.glsl:395-423)
-template <class Tracer, bool FLAT, bool COUNT>
-VRT_HD Hit trace_with_shadow(PixelCtx<FLAT, COUNT>& cx, Ray& r, V3& color) {
+template <class Tracer, bool FLAT>
+VRT_HD Hit trace_with_shadow(typename Tracer::Ctx& cx, Ray& r, V3& color) {
   Hit h = Tracer::march(cx, r);
   if (h.found) {
     cx.count(CNT_HITS);
@@ -150,7 +164,7 @@ VRT_HD Hit trace_with_shadow(PixelCtx<FLAT, COUNT>& cx, Ray& r, V3& color) {
       MatProps m = material_of<FLAT>(h.voxel);
       V3 n = cx.normal_of(h);
       float diffuse = m.kd * gmax(dot3(n, s.dir), 0.0f);
-      float specular = m.ks * powf(gmax(dot3(reflect3(s.dir, n), r.dir), 0.0f), m.ke);
+      float specular = m.ks * cx.pow_pos(gmax(dot3(reflect3(s.dir, n), r.dir), 0.0f), m.ke);
       brightness = (0.3f + diffuse) + specular;
     }
     float c[4];
@@ -169,8 +183,8 @@ struct PixelResult {
 };
 
 // Vertex stage at the pixel centre (voxel.glsl:467-475) + fragment main (voxel.glsl:425-452)
-template <class Tracer, bool FLAT, bool COUNT>
-VRT_HD PixelResult shade_pixel(PixelCtx<FLAT, COUNT>& cx, int px, int py) {
+template <class Tracer, bool FLAT>
+VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
   const vrt_params& p = cx.f.p;
   const float* m = p.invPV;
   float nx = ((float)px + 0.5f) / (float)p.width * 2.0f - 1.0f;
@@ -186,21 +200,19 @@ VRT_HD PixelResult shade_pixel(PixelCtx<FLAT, COUNT>& cx, int px, int py) {
   V3 vdir = mk3(fr[0] / fr[3] - vnear.x, fr[1] / fr[3] - vnear.y, fr[2] / fr[3] - vnear.z);
 
   constexpr int kStack = 8;  // maxReflections + maxTransparencies + 1 <= 8 (checked by the API)
-  Ray stack[kStack];
+  Ray stack[kStack];         // only bounce rays ever live here; the primary ray stays in registers
   float half = cx.f.fsize * 0.5f;
-  Ray r0;
-  r0.pos = mk3(vnear.x + half, vnear.y + half, vnear.z + half);
-  r0.dir = randomize_direction(normalize3(vdir), vnear, p.rayNoise, p.time);
-  r0.len = 0.0f; r0.energy = 1.0f; r0.medium = 0; r0.nrefl = 0; r0.ntrans = 0; r0.face_axis = -1; r0.face_nsign = 0.0f;
-  stack[0] = r0;
-  int n = 1, popped = 0;
+  Ray r;
+  r.pos = mk3(vnear.x + half, vnear.y + half, vnear.z + half);
+  r.dir = cx.jitter(normalize3(vdir), vnear, p.rayNoise);
+  r.len = 0.0f; r.energy = 1.0f; r.medium = 0; r.nrefl = 0; r.ntrans = 0; r.face_axis = -1; r.face_nsign = 0.0f;
+  int n = 0, popped = 0;
   V3 color = mk3(0.0f, 0.0f, 0.0f);
   PixelResult out;
   out.hit = VRT_HIT_MISS;
-  while (n > 0) {
-    Ray r = stack[--n];
+  for (;;) {                 // LIFO order of voxel.glsl:434-449: the refraction ray is traced before the reflection ray
     cx.count(popped == 0 ? CNT_PRIMARY : CNT_SECONDARY);
-    Hit h = trace_with_shadow<Tracer, FLAT, COUNT>(cx, r, color);
+    Hit h = trace_with_shadow<Tracer, FLAT>(cx, r, color);
     if (popped == 0 && h.found) out.hit = h.cell;
     popped++;
     if (h.found) {
@@ -212,6 +224,8 @@ VRT_HD PixelResult shade_pixel(PixelCtx<FLAT, COUNT>& cx, int px, int py) {
         if (c[3] != 1.0f && n < kStack) stack[n++] = cx.refraction_of(r, h);
       }
     }
+    if (n == 0) break;
+    r = stack[--n];
   }
   out.rgba[0] = color.x; out.rgba[1] = color.y; out.rgba[2] = color.z; out.rgba[3] = 1.0f;
   out.bounces = popped;

@@ -14,7 +14,7 @@ namespace vrt {
 
 template <bool FLAT, bool COUNT>
 struct ExactTracer {
-  typedef PixelCtx<FLAT, COUNT> Ctx;
+  typedef PixelCtx<FLAT, COUNT, false> Ctx;
 
   // nextPlane (voxel.glsl:263-266, 306-309)
   static VRT_HD V3 first_planes(const V3& q, const V3& d) {

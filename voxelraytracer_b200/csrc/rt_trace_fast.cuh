@@ -41,100 +41,79 @@ VRT_HD uint32_t load_cell(const uint16_t* cells, uint32_t idx) {
 
 template <bool FLAT, bool COUNT>
 struct FastTracer {
-  typedef PixelCtx<FLAT, COUNT> Ctx;
+  typedef PixelCtx<FLAT, COUNT, true> Ctx;
 
+  // Position-dependent state of a walk; the direction constants are referenced, not copied, so that the
+  // shadow rays read them straight from the kernel's constant bank.
   struct Walk {
-    V3 o, d, inv;          // origin, direction, 1/direction (+inf where d == 0)
-    V3 tmax, tdel;         // next plane crossing time per axis / time per cell (0 where d == 0)
-    V3 off;                // 1 where d >= 0 else 0: the next plane of cell c is c + off
-    float invmax;          // 1 / max |d|
-    float jbias;           // (1 + 1/64) * invmax: a jump advances by r * invmax - jbias
-    int dix, diy, diz;     // padded-index increment per axis step
+    V3 o;                  // origin
+    V3 tmax;               // next plane crossing time per axis (+inf where d == 0)
     uint32_t idx;          // padded index of the current cell
-    uint32_t ibias;        // constant folded into the jump's index computation (device path)
     float t, tprev;        // entry time of the current cell / of its predecessor
-    bool sx, sy;           // last plane crossed: x / y / (neither) z
-    bool zx, zy, zz;       // d == 0 per axis
+    int ax;                // last plane crossed: 0 x, 1 y, 2 z
   };
 
-  static VRT_HD float finf() { return u2f(0x7F800000u); }
-  static VRT_HD int last_axis(const Walk& w) { return w.sx ? 0 : (w.sy ? 1 : 2); }
-
-  // Sets the direction-dependent constants.
-  static VRT_HD void set_dir(Walk& w, const V3& o, const V3& d, int P) {
-    w.o = o; w.d = d;
-    w.zx = d.x == 0.0f; w.zy = d.y == 0.0f; w.zz = d.z == 0.0f;
-    // For a zero component: inv = +inf and off = 1, so (floor(o) + 1 - o) * inv = +inf, never NaN, never the minimum.
-    w.inv = mk3(w.zx ? finf() : 1.0f / d.x, w.zy ? finf() : 1.0f / d.y, w.zz ? finf() : 1.0f / d.z);
-    w.tdel = mk3(w.zx ? 0.0f : fabsf(w.inv.x), w.zy ? 0.0f : fabsf(w.inv.y), w.zz ? 0.0f : fabsf(w.inv.z));
-    w.off = mk3(d.x >= 0.0f ? 1.0f : 0.0f, d.y >= 0.0f ? 1.0f : 0.0f, d.z >= 0.0f ? 1.0f : 0.0f);
-    w.invmax = 1.0f / fmaxf(fabsf(d.x), fmaxf(fabsf(d.y), fabsf(d.z)));
-    w.jbias = 1.015625f * w.invmax;
-    w.dix = d.x > 0.0f ? 1 : -1;
-    w.diy = d.y > 0.0f ? P : -P;
-    w.diz = d.z > 0.0f ? P * P : -(P * P);
-    // float->int by magic number: bits(q + 1.5*2^23, rounded down) = 0x4B400000 + floor(q); fold "+1" per axis too
-    w.ibias = (uint32_t)(0x4B400000u - 1u) * (uint32_t)(P * P + P + 1);
-    w.sx = false; w.sy = false;
-  }
-
   // Places the walk in cell (cx,cy,cz) (unpadded integer coordinates, -1..n allowed) and derives the plane
-  // times from the cell, with IEEE division like the shader's t = (nextPlane - pos) / dir.
-  static VRT_HD void set_cell(Walk& w, float cx, float cy, float cz, int P) {
+  // times from the cell: t = (nextPlane - pos) * (1 / dir).
+  static VRT_HD void set_cell(Walk& w, const DirConst& k, float cx, float cy, float cz, int P) {
     w.idx = (uint32_t)(((int)cz + 1) * P + ((int)cy + 1)) * (uint32_t)P + (uint32_t)((int)cx + 1);
-    w.tmax.x = w.zx ? finf() : ((cx + w.off.x) - w.o.x) / w.d.x;
-    w.tmax.y = w.zy ? finf() : ((cy + w.off.y) - w.o.y) / w.d.y;
-    w.tmax.z = w.zz ? finf() : ((cz + w.off.z) - w.o.z) / w.d.z;
+    w.tmax.x = k.tdel.x == 0.0f ? finf() : ((cx + k.off.x) - w.o.x) * k.inv.x;
+    w.tmax.y = k.tdel.y == 0.0f ? finf() : ((cy + k.off.y) - w.o.y) * k.inv.y;
+    w.tmax.z = k.tdel.z == 0.0f ? finf() : ((cz + k.off.z) - w.o.z) * k.inv.z;
   }
 
-  // One Amanatides-Woo step: cross the nearest plane (ties: x before y before z).
-  static VRT_HD void step(Walk& w) {
+  // One Amanatides-Woo step: cross the nearest plane (ties: x before y before z).  Written with selects so that
+  // it compiles to straight-line predicated code (tdel is finite; adding 0 is exact).
+  static VRT_HD void step(Walk& w, const DirConst& k) {
     const float m = fminf(w.tmax.x, fminf(w.tmax.y, w.tmax.z));
     const bool sx = w.tmax.x == m;
     const bool sy = !sx && w.tmax.y == m;
+    const bool sz = !sx && !sy;
     w.tprev = w.t;
     w.t = m;
-    if (sx) { w.idx += (uint32_t)w.dix; w.tmax.x += w.tdel.x; }
-    else if (sy) { w.idx += (uint32_t)w.diy; w.tmax.y += w.tdel.y; }
-    else { w.idx += (uint32_t)w.diz; w.tmax.z += w.tdel.z; }
-    w.sx = sx; w.sy = sy;
+    w.idx += (uint32_t)(sx ? k.dix : (sy ? k.diy : k.diz));
+    w.tmax.x += sx ? k.tdel.x : 0.0f;
+    w.tmax.y += sy ? k.tdel.y : 0.0f;
+    w.tmax.z += sz ? k.tdel.z : 0.0f;
+    w.ax = sx ? 0 : (sy ? 1 : 2);
   }
 
   // Jump inside the empty cube promised by radius r (r >= 2): advance by (r - 1 - 1/64) cells of dominant-axis
   // travel, then re-derive the cell and the plane times from the position.  False if the length cap forbids it.
-  static VRT_HD bool jump(Walk& w, uint32_t r, float tcap, int P) {
+  static VRT_HD bool jump(Walk& w, const DirConst& k, uint32_t r, float tcap, int P) {
     // (float)r without a conversion instruction: 2^23 + r has r in its low mantissa bits
     const float rf = u2f(0x4B000000u | r) - 8388608.0f;
-    const float tn = fmaf(rf, w.invmax, w.t - w.jbias);
+    const float tn = fmaf(rf, k.invmax, w.t - k.jbias);
     if (!(tn < tcap)) return false;
-    const float qx = fmaf(tn, w.d.x, w.o.x), qy = fmaf(tn, w.d.y, w.o.y), qz = fmaf(tn, w.d.z, w.o.z);
+    const float qx = fmaf(tn, k.d.x, w.o.x), qy = fmaf(tn, k.d.y, w.o.y), qz = fmaf(tn, k.d.z, w.o.z);
 #if defined(__CUDA_ARCH__)
     // floor + float->int on the FMA/ALU pipes: add 1.5*2^23 rounding DOWN; the sum's low bits are floor(q)
     const float mx = __fadd_rd(qx, 12582912.0f), my = __fadd_rd(qy, 12582912.0f), mz = __fadd_rd(qz, 12582912.0f);
     const float fx = mx - 12582912.0f, fy = my - 12582912.0f, fz = mz - 12582912.0f;
-    w.idx = (f2u(mz) * (uint32_t)P + f2u(my)) * (uint32_t)P + f2u(mx) - w.ibias;
+    w.idx = (f2u(mz) * (uint32_t)P + f2u(my)) * (uint32_t)P + f2u(mx) - k.ibias;
 #else
     const float fx = floorf(qx), fy = floorf(qy), fz = floorf(qz);
     w.idx = (uint32_t)(((int)fz + 1) * P + ((int)fy + 1)) * (uint32_t)P + (uint32_t)((int)fx + 1);
 #endif
-    w.tmax.x = ((fx + w.off.x) - w.o.x) * w.inv.x;
-    w.tmax.y = ((fy + w.off.y) - w.o.y) * w.inv.y;
-    w.tmax.z = ((fz + w.off.z) - w.o.z) * w.inv.z;
+    w.tmax.x = ((fx + k.off.x) - w.o.x) * k.inv.x;
+    w.tmax.y = ((fy + k.off.y) - w.o.y) * k.inv.y;
+    w.tmax.z = ((fz + k.off.z) - w.o.z) * k.inv.z;
     w.tprev = w.t;
     w.t = tn;
     return true;
   }
 
   // Moves from an empty (or untested start) cell with radius r to the next cell that must be looked at.
-  static VRT_HD void advance(Walk& w, uint32_t r, float tcap, int P) {
-    if (r >= (uint32_t)VRT_JUMP_MIN && jump(w, r, tcap, P)) return;
-    step(w);
-    if (r >= 2u) step(w);
+  static VRT_HD void advance(Walk& w, const DirConst& k, uint32_t r, float tcap, int P) {
+    if (r >= (uint32_t)VRT_JUMP_MIN && jump(w, k, r, tcap, P)) return;
+    step(w, k);
+    if (r >= 2u) step(w, k);
   }
 
   // Start of a ray.  Returns false when the ray can never touch the chunk.
-  static VRT_HD bool begin(Walk& w, const Ray& r, float fsize, int n, int P) {
-    set_dir(w, r.pos, r.dir, P);
+  static VRT_HD bool begin(Walk& w, const DirConst& k, const Ray& r, float fsize, int n, int P) {
+    w.o = r.pos;
+    w.ax = 2;
     const float fn1 = (float)(n - 1);
     if (r.face_axis >= 0) {
       // Spawned on a voxel face: the start cell is the one on the parent ray's side of the face, taken from
@@ -143,49 +122,47 @@ struct FastTracer {
       const int a = r.face_axis;
       float plane = rintf(vget(r.pos, a));
       c[a] = r.face_nsign > 0.0f ? plane : plane - 1.0f;
-      for (int k = 0; k < 3; k++) c[k] = fminf(fmaxf(c[k], k == a ? -1.0f : 0.0f), k == a ? (float)n : fn1);
-      float da = vget(r.dir, a);
+      for (int j = 0; j < 3; j++) c[j] = fminf(fmaxf(c[j], j == a ? -1.0f : 0.0f), j == a ? (float)n : fn1);
+      float da = vget(k.d, a);
       bool into = da != 0.0f && (da > 0.0f) != (r.face_nsign > 0.0f);  // moving against the normal = through the face
       if ((c[a] < 0.0f || c[a] > fn1) && !into) return false;          // on the chunk boundary, heading out
-      set_cell(w, c[0], c[1], c[2], P);
-      if (da != 0.0f) {
-        float far_plane = da > 0.0f ? c[a] + 1.0f : c[a];
-        vset(w.tmax, a, into ? 0.0f : (far_plane - vget(r.pos, a)) / da);
-      }
+      set_cell(w, k, c[0], c[1], c[2], P);
+      if (into) vset(w.tmax, a, 0.0f);
       w.t = 0.0f; w.tprev = 0.0f;
       return true;
     }
     bool inside = r.pos.x >= 0.0f && r.pos.x <= fsize && r.pos.y >= 0.0f && r.pos.y <= fsize && r.pos.z >= 0.0f && r.pos.z <= fsize;
     if (inside) {
-      set_cell(w, fminf(floorf(r.pos.x), fn1), fminf(floorf(r.pos.y), fn1), fminf(floorf(r.pos.z), fn1), P);
+      set_cell(w, k, fminf(floorf(r.pos.x), fn1), fminf(floorf(r.pos.y), fn1), fminf(floorf(r.pos.z), fn1), P);
       w.t = 0.0f; w.tprev = 0.0f;
       return true;
     }
     // Outside: slab test; the walk starts in the border cell in front of the entry face so that the first
     // step crosses into the chunk and the entered cell is tested like any other.
     float lo[3], hi[3];
-    for (int k = 0; k < 3; k++) {
-      float ok = vget(r.pos, k), dk = vget(r.dir, k);
-      if (dk == 0.0f) {
-        if (ok < 0.0f || ok > fsize) return false;
-        lo[k] = -finf(); hi[k] = finf();
+    for (int j = 0; j < 3; j++) {
+      float oj = vget(r.pos, j), dj = vget(k.d, j);
+      if (dj == 0.0f) {
+        if (oj < 0.0f || oj > fsize) return false;
+        lo[j] = -finf(); hi[j] = finf();
       } else {
-        float t0 = (0.0f - ok) / dk, t1 = (fsize - ok) / dk;
-        lo[k] = fminf(t0, t1); hi[k] = fmaxf(t0, t1);
+        float ij = vget(k.inv, j);
+        float t0 = (0.0f - oj) * ij, t1 = (fsize - oj) * ij;
+        lo[j] = fminf(t0, t1); hi[j] = fmaxf(t0, t1);
       }
     }
     float tin = fmaxf(lo[0], fmaxf(lo[1], lo[2])), tout = fminf(hi[0], fminf(hi[1], hi[2]));
     if (!(tin < tout) || !(tout > 0.0f)) return false;
     int ea = lo[0] >= lo[1] && lo[0] >= lo[2] ? 0 : (lo[1] >= lo[2] ? 1 : 2);
-    float q[3] = {r.pos.x + tin * r.dir.x, r.pos.y + tin * r.dir.y, r.pos.z + tin * r.dir.z};
+    float q[3] = {r.pos.x + tin * k.d.x, r.pos.y + tin * k.d.y, r.pos.z + tin * k.d.z};
     float c[3];
-    for (int k = 0; k < 3; k++) c[k] = fminf(fmaxf(floorf(q[k]), 0.0f), fn1);
-    c[ea] = vget(r.dir, ea) > 0.0f ? -1.0f : (float)n;
-    set_cell(w, c[0], c[1], c[2], P);
+    for (int j = 0; j < 3; j++) c[j] = fminf(fmaxf(floorf(q[j]), 0.0f), fn1);
+    c[ea] = vget(k.d, ea) > 0.0f ? -1.0f : (float)n;
+    set_cell(w, k, c[0], c[1], c[2], P);
     vset(w.tmax, ea, tin);
     // entry time of the border cell = the latest plane crossing before tin (>= 0)
-    float e0 = w.tmax.x - w.tdel.x, e1 = w.tmax.y - w.tdel.y, e2 = w.tmax.z - w.tdel.z;
-    float te = fmaxf(0.0f, fmaxf(w.zx ? 0.0f : e0, fmaxf(w.zy ? 0.0f : e1, w.zz ? 0.0f : e2)));
+    float e0 = w.tmax.x - k.tdel.x, e1 = w.tmax.y - k.tdel.y, e2 = w.tmax.z - k.tdel.z;
+    float te = fmaxf(0.0f, fmaxf(k.tdel.x == 0.0f ? 0.0f : e0, fmaxf(k.tdel.y == 0.0f ? 0.0f : e1, k.tdel.z == 0.0f ? 0.0f : e2)));
     w.t = fminf(te, tin); w.tprev = w.t;
     return true;
   }
@@ -196,26 +173,35 @@ struct FastTracer {
     return (x - 1u) + ((y - 1u) << log2n) + ((z - 1u) << (2 * log2n));
   }
 
+  // Walks through air from the current cell (radius `rad`, never tested itself) to the next cell with radius 0
+  // (occupied or border) and returns that cell's value; returns 0xFFFFFFFF when the length cap ends the walk first.
+  // This is the hot loop of the whole path: one 2-byte load per iteration, nothing else touches memory.
+  static VRT_HD uint32_t walk_air(Ctx& cx, Walk& w, const DirConst& k, const uint16_t* cells, uint32_t rad, float tcap, int P) {
+    for (;;) {
+      if (!(w.t < tcap)) return 0xFFFFFFFFu;
+      advance(w, k, rad, tcap, P);
+      cx.count(CNT_ACTUAL_STEPS);
+      const uint32_t c = load_cell(cells, w.idx);
+      rad = c >> 8;
+      if (rad == 0u) return c;
+    }
+  }
+
   static VRT_HD bool shadow(Ctx& cx, const Ray& r, const Hit&) {
     cx.count(CNT_SHADOW);
     const int n = cx.f.p.size, P = n + 2;
     const uint16_t* cells = cx.f.cells;
     const float tcap = cx.f.p.maxRayLength - r.len;
+    const DirConst& k = cx.f.sun;                          // shadow rays all point at the sun (voxel.glsl:191-201)
     Walk w;
-    if (!begin(w, r, cx.f.fsize, n, P)) return false;
+    if (!begin(w, k, r, cx.f.fsize, n, P)) return false;
     uint32_t rad = load_cell(cells, w.idx) >> 8;
     for (;;) {
-      if (!(w.t < tcap)) return false;
-      advance(w, rad, tcap, P);
-      cx.count(CNT_ACTUAL_STEPS);
-      uint32_t c = load_cell(cells, w.idx);
-      rad = c >> 8;
-      if (rad == 0u) {
-        uint32_t b = c & 0xFFu;
-        if (b == 0u) return false;                         // border: left the chunk
-        if (!(w.tprev < tcap)) return false;               // the shader would not have taken this step
-        if (!is_transparent((int)b)) return true;          // glass casts no shadow (voxel.glsl:288-295)
-      }
+      const uint32_t c = walk_air(cx, w, k, cells, rad, tcap, P);
+      if (c == 0xFFFFFFFFu || c == 0u) return false;       // length cap / border: left the chunk
+      if (!(w.tprev < tcap)) return false;                 // the shader would not have taken this step
+      if (!is_transparent((int)c)) return true;            // glass casts no shadow (voxel.glsl:288-295)
+      rad = 0u;                                            // glass: one plain step onwards
     }
   }
 
@@ -224,31 +210,35 @@ struct FastTracer {
     h.found = false;
     const int n = cx.f.p.size, P = n + 2;
     const uint16_t* cells = cx.f.cells;
+    DirConst k;
+    set_dir_const(k, r.dir, P);
     Walk w;
-    if (!begin(w, r, cx.f.fsize, n, P)) return h;
+    if (!begin(w, k, r, cx.f.fsize, n, P)) return h;
     float tcap = cx.f.p.maxRayLength - r.len;
     int medium = r.medium;
     int tir = 0;
     uint32_t rad = load_cell(cells, w.idx) >> 8;
     for (;;) {
-      if (!(w.t < tcap)) return h;
-      if (medium == 0) advance(w, rad, tcap, P); else step(w);
-      cx.count(CNT_ACTUAL_STEPS);
-      uint32_t c = load_cell(cells, w.idx);
-      rad = c >> 8;
-      if (rad != 0u && medium == 0) continue;              // empty cell, in air: keep walking
-      int b = (int)(c & 0xFFu);
-      if (!(w.tprev < tcap)) return h;                     // the shader would not have taken this step
-      bool is_hit = b > 0 && b != medium;
-      bool leaves = medium != 0 && b == 0;
-      if (!is_hit && !leaves) {
-        if (c == 0u) return h;                             // border while in air: left the chunk
-        continue;                                          // same medium: keep walking
+      uint32_t c;
+      if (medium == 0) {
+        c = walk_air(cx, w, k, cells, rad, tcap, P);
+        if (c == 0xFFFFFFFFu || c == 0u) return h;         // length cap / border while in air: left the chunk
+      } else {
+        // inside a transparent medium (glass): plain steps until the voxel byte changes
+        do {
+          if (!(w.t < tcap)) return h;
+          step(w, k);
+          cx.count(CNT_ACTUAL_STEPS);
+          c = load_cell(cells, w.idx);
+        } while ((int)(c & 0xFFu) == medium);
       }
+      const int b = (int)(c & 0xFFu);
+      if (!(w.tprev < tcap)) return h;                     // the shader would not have taken this step
+      const bool is_hit = b > 0;                           // b != medium holds on both paths
       h.voxel = b;
       h.point = mk3(r.pos.x + w.t * r.dir.x, r.pos.y + w.t * r.dir.y, r.pos.z + w.t * r.dir.z);
       h.len = r.len + w.t;
-      h.axis = last_axis(w);
+      h.axis = w.ax;
       h.nsign = -sign1(vget(r.dir, h.axis));
       cx.tex_coord(h.point, h.axis, b, &h.u, &h.v);
       if (is_hit) {
@@ -269,7 +259,8 @@ struct FastTracer {
       if (c == 0u && medium == 0) return h;                // refracted out through the chunk boundary
       // Restart the walk on the face just crossed.  The cell on the parent side is the medium cell the ray
       // was in; begin() derives it from face_nsign (the normal points back into that cell).
-      if (!begin(w, r, cx.f.fsize, n, P)) return h;
+      set_dir_const(k, r.dir, P);
+      if (!begin(w, k, r, cx.f.fsize, n, P)) return h;
       tcap = cx.f.p.maxRayLength - r.len;
       rad = 0u;                                            // first move from the restart cell: one plain step
     }

@@ -237,11 +237,8 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
     a.out_hit = ctx->d_hit; a.out_bounces = ctx->d_bounces;
   }
   if (p->flags & VRT_FLAG_COUNTERS) a.counters = ctx->d_counters;
-  a.sun_unit = normalize3(mk3(p->sunDir[0], p->sunDir[1], p->sunDir[2]));  // IEEE float ops, same bits as on the device
-  a.fsize = (float)p->size;
-  a.day = gmax(p->sunDir[1], 0.0f);
   a.rows_local = (int)(npix / p->tile_w);
-  a.log2n = ctx->log2n;
+  finish_frame_args(a);
   CU(cudaEventRecord(ctx->ev0, s));
   CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, s));
   CU(cudaEventRecord(ctx->ev1, s));
