@@ -49,9 +49,15 @@ struct FastTracer {
     V3 o;                  // origin
     V3 tmax;               // next plane crossing time per axis (+inf where d == 0)
     uint32_t idx;          // padded index of the current cell
-    float t, tprev;        // entry time of the current cell / of its predecessor
-    int ax;                // last plane crossed: 0 x, 1 y, 2 z
+    float t;               // entry time of the current cell
+    int inc;               // index increment of the last step taken: +-1 (x plane), +-P (y), +-P*P (z)
   };
+  // Axis of the last plane crossed.  A cell with radius 0 is only ever entered by step() (a jump lands inside the
+  // empty cube), so `inc` is always that of the crossing that produced a hit.
+  static VRT_HD int last_axis(const Walk& w, int P) {
+    const int a = w.inc < 0 ? -w.inc : w.inc;
+    return a == 1 ? 0 : (a == P ? 1 : 2);
+  }
 
   // Places the walk in cell (cx,cy,cz) (unpadded integer coordinates, -1..n allowed) and derives the plane
   // times from the cell: t = (nextPlane - pos) * (1 / dir).
@@ -69,13 +75,12 @@ struct FastTracer {
     const bool sx = w.tmax.x == m;
     const bool sy = !sx && w.tmax.y == m;
     const bool sz = !sx && !sy;
-    w.tprev = w.t;
     w.t = m;
-    w.idx += (uint32_t)(sx ? k.dix : (sy ? k.diy : k.diz));
-    w.tmax.x += sx ? k.tdel.x : 0.0f;
-    w.tmax.y += sy ? k.tdel.y : 0.0f;
-    w.tmax.z += sz ? k.tdel.z : 0.0f;
-    w.ax = sx ? 0 : (sy ? 1 : 2);
+    w.inc = sx ? k.dix : (sy ? k.diy : k.diz);
+    w.idx += (uint32_t)w.inc;
+    if (sx) w.tmax.x += k.tdel.x;
+    if (sy) w.tmax.y += k.tdel.y;
+    if (sz) w.tmax.z += k.tdel.z;
   }
 
   // Jump inside the empty cube promised by radius r (r >= 2): advance by (r - 1 - 1/64) cells of dominant-axis
@@ -98,22 +103,24 @@ struct FastTracer {
     w.tmax.x = ((fx + k.off.x) - w.o.x) * k.inv.x;
     w.tmax.y = ((fy + k.off.y) - w.o.y) * k.inv.y;
     w.tmax.z = ((fz + k.off.z) - w.o.z) * k.inv.z;
-    w.tprev = w.t;
     w.t = tn;
     return true;
   }
 
   // Moves from an empty (or untested start) cell with radius r to the next cell that must be looked at.
+  // Precondition: w.t < tcap.  The reference takes a step only while rayLength < u_MaxRayLength (voxel.glsl:273,317),
+  // so the second step of an r = 2 advance is taken only if the first one ended below the cap; the caller's
+  // loop-top test then ends the walk.
   static VRT_HD void advance(Walk& w, const DirConst& k, uint32_t r, float tcap, int P) {
     if (r >= (uint32_t)VRT_JUMP_MIN && jump(w, k, r, tcap, P)) return;
     step(w, k);
-    if (r >= 2u) step(w, k);
+    if (r >= 2u && w.t < tcap) step(w, k);
   }
 
   // Start of a ray.  Returns false when the ray can never touch the chunk.
   static VRT_HD bool begin(Walk& w, const DirConst& k, const Ray& r, float fsize, int n, int P) {
     w.o = r.pos;
-    w.ax = 2;
+    w.inc = 0;
     const float fn1 = (float)(n - 1);
     if (r.face_axis >= 0) {
       // Spawned on a voxel face: the start cell is the one on the parent ray's side of the face, taken from
@@ -128,13 +135,13 @@ struct FastTracer {
       if ((c[a] < 0.0f || c[a] > fn1) && !into) return false;          // on the chunk boundary, heading out
       set_cell(w, k, c[0], c[1], c[2], P);
       if (into) vset(w.tmax, a, 0.0f);
-      w.t = 0.0f; w.tprev = 0.0f;
+      w.t = 0.0f;
       return true;
     }
     bool inside = r.pos.x >= 0.0f && r.pos.x <= fsize && r.pos.y >= 0.0f && r.pos.y <= fsize && r.pos.z >= 0.0f && r.pos.z <= fsize;
     if (inside) {
       set_cell(w, k, fminf(floorf(r.pos.x), fn1), fminf(floorf(r.pos.y), fn1), fminf(floorf(r.pos.z), fn1), P);
-      w.t = 0.0f; w.tprev = 0.0f;
+      w.t = 0.0f;
       return true;
     }
     // Outside: slab test; the walk starts in the border cell in front of the entry face so that the first
@@ -163,7 +170,7 @@ struct FastTracer {
     // entry time of the border cell = the latest plane crossing before tin (>= 0)
     float e0 = w.tmax.x - k.tdel.x, e1 = w.tmax.y - k.tdel.y, e2 = w.tmax.z - k.tdel.z;
     float te = fmaxf(0.0f, fmaxf(k.tdel.x == 0.0f ? 0.0f : e0, fmaxf(k.tdel.y == 0.0f ? 0.0f : e1, k.tdel.z == 0.0f ? 0.0f : e2)));
-    w.t = fminf(te, tin); w.tprev = w.t;
+    w.t = fminf(te, tin);
     return true;
   }
 
@@ -178,8 +185,12 @@ struct FastTracer {
   // This is the hot loop of the whole path: one 2-byte load per iteration, nothing else touches memory.
   static VRT_HD uint32_t walk_air(Ctx& cx, Walk& w, const DirConst& k, const uint16_t* cells, uint32_t rad, float tcap, int P) {
     for (;;) {
-      if (!(w.t < tcap)) return 0xFFFFFFFFu;
-      advance(w, k, rad, tcap, P);
+      // a successful jump implies w.t < tn < tcap, so only the stepping path tests the cap itself
+      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tcap, P))) {
+        if (!(w.t < tcap)) return 0xFFFFFFFFu;
+        step(w, k);
+        if (rad >= 2u && w.t < tcap) step(w, k);
+      }
       cx.count(CNT_ACTUAL_STEPS);
       const uint32_t c = load_cell(cells, w.idx);
       rad = c >> 8;
@@ -199,7 +210,6 @@ struct FastTracer {
     for (;;) {
       const uint32_t c = walk_air(cx, w, k, cells, rad, tcap, P);
       if (c == 0xFFFFFFFFu || c == 0u) return false;       // length cap / border: left the chunk
-      if (!(w.tprev < tcap)) return false;                 // the shader would not have taken this step
       if (!is_transparent((int)c)) return true;            // glass casts no shadow (voxel.glsl:288-295)
       rad = 0u;                                            // glass: one plain step onwards
     }
@@ -233,12 +243,11 @@ struct FastTracer {
         } while ((int)(c & 0xFFu) == medium);
       }
       const int b = (int)(c & 0xFFu);
-      if (!(w.tprev < tcap)) return h;                     // the shader would not have taken this step
       const bool is_hit = b > 0;                           // b != medium holds on both paths
       h.voxel = b;
       h.point = mk3(r.pos.x + w.t * r.dir.x, r.pos.y + w.t * r.dir.y, r.pos.z + w.t * r.dir.z);
       h.len = r.len + w.t;
-      h.axis = w.ax;
+      h.axis = last_axis(w, P);
       h.nsign = -sign1(vget(r.dir, h.axis));
       cx.tex_coord(h.point, h.axis, b, &h.u, &h.v);
       if (is_hit) {
