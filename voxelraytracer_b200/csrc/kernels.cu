@@ -9,8 +9,26 @@
 
 namespace vrt {
 
-constexpr int kWarpW = 8, kWarpH = 4;       // pixels per warp patch
-constexpr int kCtaWarpsX = 2, kCtaWarpsY = 2;
+// Tunables (swept on the B200, see profiles/): warp patch, warps per CTA, minimum resident CTAs per SM.
+#ifndef VRT_WARP_W
+#define VRT_WARP_W 8
+#endif
+#ifndef VRT_CTA_WX
+#define VRT_CTA_WX 2
+#endif
+#ifndef VRT_CTA_WY
+#define VRT_CTA_WY 2
+#endif
+#ifndef VRT_MIN_BLOCKS
+#define VRT_MIN_BLOCKS 12   // 40 registers, 48 warps/SM: the kernel is issue-bound and gains from more eligible warps (sweep2)
+#endif
+#if VRT_MIN_BLOCKS > 0
+#define VRT_BOUNDS __launch_bounds__(kThreads, VRT_MIN_BLOCKS)
+#else
+#define VRT_BOUNDS __launch_bounds__(kThreads)
+#endif
+constexpr int kWarpW = VRT_WARP_W, kWarpH = 32 / VRT_WARP_W;       // pixels per warp patch
+constexpr int kCtaWarpsX = VRT_CTA_WX, kCtaWarpsY = VRT_CTA_WY;
 constexpr int kCtaW = kWarpW * kCtaWarpsX, kCtaH = kWarpH * kCtaWarpsY;
 constexpr int kThreads = 32 * kCtaWarpsX * kCtaWarpsY;
 
@@ -44,7 +62,7 @@ __device__ __forceinline__ void render_one(const FrameArgs& f, int lx, int ly) {
 }
 
 template <class Tracer, bool FLAT, bool DEBUG>
-__global__ void __launch_bounds__(kThreads) render_kernel(const __grid_constant__ FrameArgs f) {
+__global__ void VRT_BOUNDS render_kernel(const __grid_constant__ FrameArgs f) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int lx = blockIdx.x * kCtaW + (warp % kCtaWarpsX) * kWarpW + (lane & (kWarpW - 1));
   const int ly = blockIdx.y * kCtaH + (warp / kCtaWarpsX) * kWarpH + (lane / kWarpW);
