@@ -41,6 +41,8 @@ WORKLOAD_DESC = {
     "c1": "_GLASS_CUBE + _HIGH_PERFORMANCE + _COLOR_ONLY 32^3, 400x400 (BASELINE configs[0])",
 }
 I_STEP = 16          # algorithmic thread-instructions per reference DDA step
+# dram__bytes_read.sum + dram__bytes_write.sum per render_kernel launch from the committed `ncu --set full` capture (profiles/)
+NCU_TRAFFIC = {"c2": 2.8e6}
 
 
 def parse():
@@ -51,7 +53,11 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
-    ap.add_argument("--gather", default="nccl", choices=["nccl", "none"])
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl", "none"],
+                    help="N>1: p2p = every rank's render kernel stores straight into rank 0's frame over NVLink (fused render+gather); "
+                         "nccl = all_gather_into_tensor after the render; none = frames stay on their GPUs")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: one full frame per GPU per step (pose batch); strong: ONE frame per step, 16-row bands dealt round-robin")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -125,64 +131,84 @@ def run_reference(args):
                          "sample": "every %dth 12-row strip of each frame (1/%d of the scanlines), rays counted on the same strips" % (every, every)},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
 # ------------------------------------------------------------------ clocks
 class ClockSampler:
-    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
-        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    """Polls NVML (SM clock, throttle reasons, power) every ~2 ms from a thread while the timed region runs."""
 
     def __init__(self, index):
-        self.rows = []
-        self.proc = None
         self.index = index
+        self.rows = []
+        self.stop_flag = False
+        self.th = None
+        self.err = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.th = threading.Thread(target=self._read, daemon=True)
+            import pynvml as nv
+            nv.nvmlInit()
+            self.nv = nv
+            self.h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_sm = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            self.th = threading.Thread(target=self._run, daemon=True)
             self.th.start()
-        except Exception:
-            self.proc = None
+        except Exception as e:       # no NVML: report it, never fake a clock
+            self.err = repr(e)
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append(line.strip())
-
-    def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            f = [x.strip() for x in r.split(",")]
-            if len(f) < 7:
-                continue
+    def _run(self):
+        nv = self.nv
+        while not self.stop_flag:
             try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "samples": len(sm),
-                "reasons": sorted(reasons)}
+                self.rows.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM), nv.nvmlDeviceGetCurrentClocksEventReasons(self.h),
+                                  nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0))
+            except Exception as e:
+                self.err = repr(e)
+                return
+            time.sleep(0.002)
+
+    def mark(self):
+        return len(self.rows)
+
+    def stop(self, first=0, last=None):
+        self.stop_flag = True
+        if self.th:
+            self.th.join(timeout=2)
+        rows = self.rows[first:last] or self.rows
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: %s" % self.err]}
+        nv = self.nv
+        bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksEventReasonHwThermalSlowdown,
+                "sw_thermal_slowdown": nv.nvmlClocksEventReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksEventReasonSwPowerCap}
+        reasons = sorted(k for k, b in bits.items() if any(r[1] & b for r in rows))
+        return {"sm_mhz": float(np.median([r[0] for r in rows])), "sm_max_mhz": float(self.max_sm), "samples": len(rows),
+                "power_w_max": max(r[2] for r in rows), "reasons": reasons, "how": "NVML polled every ~2 ms during the timed region"}
 
 
 # ------------------------------------------------------------------ our arm
+def nvml_index(torch, local):
+    """NVML index of CUDA device `local` (CUDA_VISIBLE_DEVICES may renumber)."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        want = "GPU-" + str(torch.cuda.get_device_properties(local).uuid)
+        for i in range(nv.nvmlDeviceGetCount()):
+            u = nv.nvmlDeviceGetUUID(nv.nvmlDeviceGetHandleByIndex(i))
+            if (u.decode() if isinstance(u, bytes) else u) == want:
+                return i
+    except Exception:
+        pass
+    return local
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
     import common
     import voxelraytracer_b200 as vrt
+    from voxelraytracer_b200 import sharding
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -199,11 +225,19 @@ def run_ours(args):
     ctx.upload_atlas(atlas, ts)
     if args.mode == "exact":
         flags |= vrt.FLAG_EXACT
-    # each rank takes its own pose sequence (weak scaling: one frame per rank per step)
-    frames = [common.make_params(W, H, sc, poses[(i + rank) % len(poses)], flags) for i in range(len(poses))]
+    strong = args.scaling == "strong" and world > 1
+    gather = args.gather if world > 1 else "none"
+    BR = 16
     npix = W * H
+    frame_bytes = npix * 4
+    if strong:      # ONE frame per step: every rank renders its 16-row bands of the same pose
+        full = [common.make_params(W, H, sc, poses[i % len(poses)], flags) for i in range(len(poses))]
+        frames = [sharding.band_params(p, rank, world, BR) for p in full]
+    else:           # one full frame per rank per step, each rank on its own pose sequence
+        frames = [common.make_params(W, H, sc, poses[(i + rank) % len(poses)], flags) for i in range(len(poses))]
+    my_pix = vrt.tile_pixels(frames[0])
 
-    # reference-equivalent ray / step counts per pose (exact kernel's counters == oracle's, see tests)
+    # reference-equivalent ray / step counts of what THIS rank renders (exact kernel's counters == oracle's, see tests)
     counts = []
     for p in frames:
         q = p.copy()
@@ -217,101 +251,162 @@ def run_ours(args):
         a = ctx.counters()
         counts.append({"rays": c["primary_rays"] + c["secondary_rays"] + c["shadow_rays"], "steps": c["march_steps"] + c["shadow_steps"],
                        "hits": c["hits"], "actual": a["actual_steps"]})
-    launches0 = ctx.kernel_launches()
 
     stream = torch.cuda.Stream()
     comm = torch.cuda.Stream()
-    fb = [torch.empty((H, W, 4), dtype=torch.uint8, device="cuda") for _ in range(2)]     # double-buffered frame
-    gathered = torch.empty((world * H, W, 4), dtype=torch.uint8, device="cuda") if world > 1 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")                        # > 126 MB L2
-    do_gather = world > 1 and args.gather == "nccl"
+    token = torch.zeros(1, dtype=torch.int32, device="cuda")
+    slots = 1 if strong else world                                                          # frames held by rank 0 per step
+    local_fb = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(2)]
+    gathered = None
+    p2p_base = None
+    if gather == "p2p":
+        # rank 0 owns the gathered frames (double-buffered); the others map them through CUDA IPC and store into them
+        if rank == 0:
+            p2p_base, handle = ctx.ipc_alloc_frame(2 * slots * frame_bytes)
+            box = [handle]
+        else:
+            box = [None]
+        dist.broadcast_object_list(box, src=0)
+        if rank != 0:
+            p2p_base = ctx.ipc_open(box[0])
+        p2p_base = int(p2p_base.value)
+    elif gather == "nccl":
+        per = sharding.max_rows(H, world, BR) * W * 4 if strong else frame_bytes
+        gathered = torch.empty(world * per, dtype=torch.uint8, device="cuda")
+        local_fb = [torch.zeros(per, dtype=torch.uint8, device="cuda") for _ in range(2)]
+
+    def target(i):
+        """(params, device pointer) of step i's output for this rank."""
+        p = frames[i % len(frames)]
+        if gather == "p2p":
+            if strong:
+                q = p.copy()
+                q.flags |= vrt.FLAG_OUT_FRAME          # bands land at their frame rows inside rank 0's frame
+                return q, p2p_base + (i % 2) * frame_bytes
+            return p, p2p_base + ((i % 2) * world + rank) * frame_bytes
+        return p, local_fb[i % 2].data_ptr()
 
     def one_step(i, ev0=None, ev1=None, do_flush=True):
-        """flush (untimed) -> [ev0] render -> NCCL all-gather of the frames [ev1].  Returns the completion event."""
-        p = frames[i % len(frames)]
-        buf = fb[i % 2]
+        """flush (untimed) -> [ev0] render (p2p: its stores ARE the gather) (+ nccl gather) [ev1].  Returns the completion event."""
+        p, ptr = target(i)
         with torch.cuda.stream(stream):
             if do_flush:
-                flush.fill_(i & 0xFF)                # evict L2 between timed windows (window starts after it)
+                flush.fill_(i & 0xFF)                # evict L2 between timed windows (the window starts after it)
             if ev0 is not None:
                 ev0.record(stream)
-            ctx.render_to(p, buf.data_ptr(), stream.cuda_stream)
-            if ev1 is not None and not do_gather:
+            ctx.render_to(p, ptr, stream.cuda_stream)
+            if ev1 is not None and gather != "nccl":
                 ev1.record(stream)
         done = torch.cuda.Event()
-        if do_gather:
-            rendered = torch.cuda.Event()
-            rendered.record(stream)
-            with torch.cuda.stream(comm):
-                comm.wait_event(rendered)
-                dist.all_gather_into_tensor(gathered, buf)
+        if gather == "none":
+            done.record(stream)
+            return done
+        rendered = torch.cuda.Event()
+        rendered.record(stream)
+        with torch.cuda.stream(comm):
+            comm.wait_event(rendered)
+            if gather == "nccl":
+                dist.all_gather_into_tensor(gathered, local_fb[i % 2])
                 if ev1 is not None:
                     ev1.record(comm)
-                done.record(comm)
-        else:
-            done.record(stream)
+            else:
+                # p2p: 4-byte all-reduce = "every rank's stores of step i have landed in rank 0's frame"; it runs on the
+                # comm stream beside the next step's flush + render and is what rank 0's consumer would wait on
+                dist.all_reduce(token)
+            done.record(comm)
         return done
 
-    sampler = ClockSampler(local)
+    # ---- gather check (untimed): what rank 0 holds after one step equals what the ranks rendered locally
+    gather_check = None
+    if gather != "none":
+        one_step(0, do_flush=False).synchronize()
+        torch.cuda.synchronize(); dist.barrier()
+        loc = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
+        ctx.render_to(full[0] if strong else frames[0], loc.data_ptr(), None)      # strong: rank-local render of the WHOLE frame
+        torch.cuda.synchronize()
+        held = _wrap_device(torch, p2p_base, slots * frame_bytes) if (gather == "p2p" and rank == 0) else gathered
+        if strong:
+            if rank == 0:
+                if gather == "nccl":
+                    mr = sharding.max_rows(H, world, BR)
+                    perm = torch.from_numpy(sharding.row_permutation(H, world, BR)).cuda()
+                    held = held.view(world * mr, W * 4)[perm].reshape(-1)
+                gather_check = "ok" if torch.equal(held[:frame_bytes], loc) else "MISMATCH"
+        else:
+            mine = loc.to(torch.int64).sum().reshape(1)
+            sums = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(sums, mine)
+            if rank == 0:
+                ok = torch.equal(held[:frame_bytes], loc)
+                for r in range(world):
+                    ok = ok and int(held[r * frame_bytes:(r + 1) * frame_bytes].to(torch.int64).sum()) == int(sums[r])
+                gather_check = "ok" if ok else "MISMATCH"
+        dist.barrier()
+
+    sampler = ClockSampler(nvml_index(torch, local))
     if rank == 0:
-        sampler.start()                              # samples cover warm-up + the timed region (frames are ~0.1 ms each)
+        sampler.start()
     for i in range(args.warmup):
         stream.wait_event(one_step(i))
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    # Timed region: K steps, each its own CUDA-event window [render (+ gather)], L2 flushed before each window.
+    # Timed region: K steps, each its own CUDA-event window on the render stream, L2 flushed before each window.
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = ctx.kernel_launches()
+    m0 = sampler.mark()
     t_wall0 = time.perf_counter()
     for i in range(args.steps):
-        stream.wait_event(one_step(i, ev[i][0], ev[i][1]))     # no overlap between steps in this pass
+        stream.wait_event(one_step(i, ev[i][0], ev[i][1]))     # step i+1 starts after step i (and its gather / signal) finished
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     t_wall = time.perf_counter() - t_wall0
-    clocks = sampler.stop() if rank == 0 else None
-    step_ms = [a.elapsed_time(b) for a, b in ev]
-    t_steps = sum(step_ms) / 1e3
+    m1 = sampler.mark()
+    launches_timed = ctx.kernel_launches() - launches0
+    t_steps = sum(a.elapsed_time(b) for a, b in ev) / 1e3
 
-    # kernel-only windows (for the roofline): the same steps without the gather inside the window
-    if do_gather:
+    # kernel-only windows (for the roofline): the same steps without a gather inside the window
+    if gather == "nccl":
         kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
         for i in range(args.steps):
+            p, ptr = target(i)
             with torch.cuda.stream(stream):
                 flush.fill_(i & 0xFF)
                 kev[i][0].record(stream)
-                ctx.render_to(frames[i % len(frames)], fb[i % 2].data_ptr(), stream.cuda_stream)
+                ctx.render_to(p, ptr, stream.cuda_stream)
                 kev[i][1].record(stream)
         torch.cuda.synchronize()
         t_kernel = sum(a.elapsed_time(b) for a, b in kev) / 1e3
     else:
         t_kernel = t_steps
+    clocks = sampler.stop(m0, m1) if rank == 0 else None
     rays = sum(counts[i % len(frames)]["rays"] for i in range(args.steps))
     steps_ref = sum(counts[i % len(frames)]["steps"] for i in range(args.steps))
     steps_act = sum(counts[i % len(frames)]["actual"] for i in range(args.steps))
     hits = sum(counts[i % len(frames)]["hits"] for i in range(args.steps))
 
-    # Pipelined pass (informational): the gather of frame i overlaps the render of frame i+1 on the comm stream;
-    # no L2 fills here, so it is reported beside the headline, not as it.
+    # Pipelined pass (informational): no L2 fills, step i+1's render overlaps step i's gather / signal.
     t_pipeline = None
-    if do_gather:
+    if world > 1:
         torch.cuda.synchronize(); dist.barrier()
         p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         pend = []
         p0.record(stream)
         for i in range(args.steps):
             if len(pend) >= 2:
-                stream.wait_event(pend[-2])          # frame buffer i%2 was last gathered two steps ago
+                stream.wait_event(pend[-2])          # buffer i%2 was last gathered two steps ago
             pend.append(one_step(i, do_flush=False))
         stream.wait_event(pend[-1])
         p1.record(stream)
         torch.cuda.synchronize(); dist.barrier()
         t_pipeline = p0.elapsed_time(p1) / 1e3
 
-    # e2e: the host-facing call (vrt_render_host): params in, frame back in pinned host memory, every step
-    host, hp = ctx.host_alloc(npix * 4)
+    # e2e: the host-facing call (vrt_render_host): params in, this rank's pixels back in pinned host memory, every step
+    host, hp = ctx.host_alloc(my_pix * 4)
     for i in range(3):
         ctx.render_host(frames[i % len(frames)], hp, stream.cuda_stream)
     torch.cuda.synchronize()
@@ -322,19 +417,17 @@ def run_ours(args):
         ctx.render_host(frames[i % len(frames)], hp, stream.cuda_stream)
     torch.cuda.synchronize()
     t_e2e = time.perf_counter() - t0
-    launches = ctx.kernel_launches() - launches0 - 3  # minus the e2e warm-ups
 
-    # max over ranks
-    t_step_total = t_steps
+    # max over ranks for times, sum over ranks for work
     if world > 1:
-        v = torch.tensor([t_step_total, t_kernel, t_e2e, t_pipeline or 0.0], dtype=torch.float64, device="cuda")
+        v = torch.tensor([t_steps, t_kernel, t_e2e, t_pipeline or 0.0], dtype=torch.float64, device="cuda")
         dist.all_reduce(v, op=dist.ReduceOp.MAX)
         t_step_total, t_kernel_max, t_e2e, t_pipeline = [float(x) for x in v.cpu()]
         s = torch.tensor([rays, steps_ref, steps_act, hits], dtype=torch.float64, device="cuda")
         dist.all_reduce(s, op=dist.ReduceOp.SUM)
         rays_all, steps_all, act_all, hits_all = [float(x) for x in s.cpu()]
     else:
-        t_kernel_max = t_kernel
+        t_step_total, t_kernel_max = t_steps, t_kernel
         rays_all, steps_all, act_all, hits_all = float(rays), float(steps_ref), float(steps_act), float(hits)
 
     if rank == 0:
@@ -347,56 +440,99 @@ def run_ours(args):
         sms = torch.cuda.get_device_properties(local).multi_processor_count
         f_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
         p_issue = sms * 4 * 32 * f_mhz * 1e6                          # thread-instructions / s at the sampled clock
-        # dominant kernel = render_kernel; per launch (this rank): algorithmic instructions and bytes
+        # dominant kernel = render_kernel; per launch (rank 0's launches): algorithmic instructions and bytes
         per_launch_s = t_kernel / args.steps
         instr_per_launch = I_STEP * steps_ref / args.steps
-        bytes_per_launch = (steps_ref * 1 + hits * 4 + npix * 4 * args.steps) / args.steps
+        bytes_per_launch = (steps_ref * 1 + hits * 4 + my_pix * 4 * args.steps) / args.steps
         ach_issue = instr_per_launch / per_launch_s
+        frames_total = args.steps * (1 if strong else world)
+        shard = "one GPU" if world == 1 else (
+            ("ONE frame per step split into 16-row bands dealt round-robin over the ranks" if strong else "one frame per GPU per step (pose batch)")
+            + ", grid replicated; gather: " + {"p2p": "every rank's render kernel stores its pixels straight into rank 0's frame over NVLink (CUDA IPC mapping), "
+                                                      "4-byte NCCL all-reduce per step as the completion signal (overlapped)",
+                                               "nccl": "all_gather_into_tensor after the render, inside the step window", "none": "none"}[gather])
         line = {
             "metric": "Mrays/s at 1080p terrain scene" if args.workload == "c2" else "Mrays/s", "value": rays_all / t_step_total / 1e6,
             "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_step_total / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_DESC[args.workload], "poses": poses, "frame": [W, H], "traversal": args.mode,
-                       "sharding": "one frame per GPU per step (pose batch), grid replicated" + (", frames all-gathered over NCCL, overlapped" if do_gather else ""),
+            "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD_DESC[args.workload], "poses": poses, "frame": [W, H], "traversal": args.mode, "sharding": shard,
                        "l2": "flushed: 256 MiB fill before every timed step window (the fill itself is outside the window)",
                        "maxRayLength": 100.0},
-            "frames_per_s": world * args.steps / t_step_total,
-            "kernel_ms_per_frame": 1e3 * t_kernel_max / args.steps,
-            "rays_per_frame": rays_all / (world * args.steps), "ref_steps_per_frame": steps_all / (world * args.steps),
-            "actual_steps_per_frame": act_all / (world * args.steps),
+            "frames_per_s": frames_total / t_step_total,
+            "kernel_ms_per_launch": 1e3 * t_kernel_max / args.steps,
+            "rays_per_frame": rays_all / frames_total, "ref_steps_per_frame": steps_all / frames_total,
+            "actual_steps_per_frame": act_all / frames_total,
             "gsteps_per_s": steps_all / t_step_total / 1e9,
             "roofline": {"bound": "issue", "achieved": ach_issue / 1e12, "peak": p_issue / 1e12, "unit": "Tinstr/s", "frac": ach_issue / p_issue,
-                         "traffic": None, "peak_source": "148 SM x 4 schedulers x 32 lanes x sampled SM clock %.0f MHz" % f_mhz,
+                         "traffic": None, "peak_source": "%d SM x 4 schedulers x 32 lanes x sampled SM clock %.0f MHz" % (sms, f_mhz),
                          "algorithmic": "%d thread-instr per reference DDA step x reference steps (SURVEY.md 8(d))" % I_STEP},
             "roofline_hbm": {"bound": "hbm", "achieved": bytes_per_launch / per_launch_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": bytes_per_launch / per_launch_s / 1e9 / hbm_peak, "traffic": None,
-                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback"},
-            "e2e": {"value": rays_all / t_e2e / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(vrt.Params), "d2h_bytes_per_step": npix * 4,
-                    "call": "vrt_render_host (params by value, RGBA8 frame copied to pinned host memory, synchronised)"},
-            "gpu_launches": int(args.steps),          # one render_kernel launch per timed step (per rank)
-            "gpu_launches_total": int(launches),      # every kernel this process's ctx launched after setup
+                             "frac": bytes_per_launch / per_launch_s / 1e9 / hbm_peak, "traffic": NCU_TRAFFIC.get(args.workload),
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"},
+            "e2e": {"value": rays_all / t_e2e / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(vrt.Params), "d2h_bytes_per_step": my_pix * 4,
+                    "call": "vrt_render_host (params by value, RGBA8 pixels copied to pinned host memory, synchronised), per rank"},
+            "gpu_launches": int(launches_timed),      # render_kernel launches of rank 0 inside the timed region (one per step)
+            "gather_check": gather_check,
             "pipelined": None if not t_pipeline else {"value": rays_all / t_pipeline / 1e6, "unit": "Mrays/s",
-                                                       "note": "gather of frame i overlapped with render of frame i+1; no L2 fills"},
+                                                       "note": "same steps back to back, no L2 fills: step i+1's render overlaps step i's gather/signal"},
             "clocks": clocks,
             "wall_s": t_wall,
         }
         if world == 1 and not args.no_cpu_baseline:
-            threads = os.cpu_count() or 1
-            sample = strips(H)
-            p = frames[0]
-            r_s, _ = sample_rays(common, p, grid, atlas, sample, threads)
-            dt, kind = cpu_reference_frame(common, p, grid, atlas, sample, threads)
-            line["cpu_baseline"] = {"value": r_s / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
-                                    "sample": "pose %s, every 4th 12-row strip (1/4 of the scanlines), %.1f s" % (poses[0], dt)}
-        print(json.dumps(line))
+            line["cpu_baseline"] = cpu_baseline(common, frames, poses, grid, atlas)
+        emit(line)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
     ctx.close()
     return 0
 
 
+def _wrap_device(torch, ptr, nbytes):
+    """A torch uint8 view of raw device memory (used to look at the IPC frame rank 0 owns)."""
+    class _Raw:
+        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (int(ptr), False), "version": 3}
+    return torch.as_tensor(_Raw(), device="cuda")
+
+
+def cpu_baseline(common, frames, poses, grid, atlas, target_s=12.0):
+    """The reference shader (oracle/_ref) on all host cores, full frames of the recorded poses, repeated until ~target_s of CPU
+    time has been spent (at least one frame of each pose); rays counted by the oracle on the same frames, outside the timing."""
+    threads = os.cpu_count() or 1
+    use_ref = common.ref_lib() is not None
+    rays = [common.oracle_render(p, grid, atlas, nthreads=threads).counters for p in frames]
+    rays = [c["primary_rays"] + c["secondary_rays"] + c["shadow_rays"] for c in rays]
+    t_total, r_total, n = 0.0, 0, 0
+    while n < len(frames) or t_total < target_s:
+        p = frames[n % len(frames)]
+        t0 = time.perf_counter()
+        if use_ref:
+            common.ref_render(p, grid, atlas, nthreads=threads)
+        else:
+            common.oracle_render(p, grid, atlas, nthreads=threads)
+        t_total += time.perf_counter() - t0
+        r_total += rays[n % len(frames)]
+        n += 1
+        if n >= 64:
+            break
+    return {"value": r_total / t_total / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "reference" if use_ref else "port",
+            "sample": "%d full frames (poses %s cycled), %.1f s of wall time on %d threads" % (n, ",".join(poses), t_total, threads)}
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else a library prints (NCCL banners ...) went to stderr."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    global _REAL_STDOUT
     args = parse()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)                      # fd 1 -> stderr for the whole run (C libraries included)
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)

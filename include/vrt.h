@@ -43,6 +43,10 @@ enum {
                                     the brick-skipping traversal, which may differ on grazing rays only */
 #define VRT_FLAG_COUNTERS   0x8u /* accumulate ray/step counters (vrt_get_counters); slower, for tests/roofline */
 #define VRT_FLAG_FLOAT_OUT  0x10u /* also keep an unquantised float32 RGBA frame for RMS checks */
+#define VRT_FLAG_OUT_FRAME  0x20u /* vrt_render_to only: d_rgba8 is a FULL width x height frame and every pixel of the tile /
+                                     band set is stored at its frame position (row * width + x) instead of compactly.  Lets
+                                     several GPUs render disjoint tiles straight into one frame (e.g. rank 0's, mapped over
+                                     NVLink with vrt_ipc_open): the gather is the kernel's own stores. */
 
 #define VRT_HIT_MISS 0xFFFFFFFFu
 
@@ -154,6 +158,8 @@ int vrt_host_free(vrt_ctx* ctx, void* p);
 int vrt_device_alloc(vrt_ctx* ctx, size_t bytes, void** out);
 int vrt_device_free(vrt_ctx* ctx, void* p);
 int vrt_synchronize(vrt_ctx* ctx, void* stream);
+int vrt_copy_to_host(vrt_ctx* ctx, void* host, const void* d_src, size_t bytes, void* stream);   /* async on `stream`, then synchronised */
+int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes, void* stream); /* async on `stream`, then synchronised */
 
 /* ---- temporal accumulation pass (res/shaders/temporal.glsl:13-19; main.cpp:363-376,388-393) ----
  * acc = alpha * new + (1 - alpha) * acc on RGBA8 device buffers, n pixels. */

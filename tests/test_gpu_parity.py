@@ -146,3 +146,25 @@ def test_synthetic_256_and_long_rays(ctx):
     assert bad <= max(2, int(1e-4 * 640 * 360)), bad
     assert (rms255(g.rgba8, o.rgba8) <= 1.0).all()
     assert (o.hit != vrt.HIT_MISS).mean() > 0.1
+
+
+def test_out_frame_flag_writes_bands_in_place(ctx):
+    """VRT_FLAG_OUT_FRAME: band renders of several 'ranks' into ONE full-frame device buffer == the one-shot frame."""
+    from voxelraytracer_b200 import sharding
+    grid, n, atlas, ts = upload(ctx, "terrain32")
+    W, H = 322, 181                                  # ragged against the 16x8 CTA patch and the band height
+    p = make_params(W, H, "terrain32", "terrain32_above")
+    full = gpu_render(ctx, p, flags_extra=0).rgba8.reshape(H, W, 4)
+    d = ctx.device_alloc(W * H * 4)
+    try:
+        for r in range(3):
+            q = sharding.band_params(p, r, 3, 16)
+            q.flags |= vrt.FLAG_OUT_FRAME
+            ctx.render_to(q, d, None)
+        got = ctx.copy_to_host(d, W * H * 4).reshape(H, W, 4)
+        assert np.array_equal(got, full)
+    finally:
+        ctx.device_free(d)
+    with pytest.raises(vrt.VrtError):
+        q = p.copy(); q.flags |= vrt.FLAG_OUT_FRAME
+        ctx.render(q)                                 # needs vrt_render_to

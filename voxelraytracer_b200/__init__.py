@@ -14,6 +14,7 @@ from .api import (  # noqa: F401
     FLAG_DEBUG_MAPS,
     FLAG_EXACT,
     FLAG_FLOAT_OUT,
+    FLAG_OUT_FRAME,
     HIT_MISS,
     Context,
     Counters,

@@ -11,6 +11,7 @@ FLAG_DEBUG_MAPS = 0x2
 FLAG_EXACT = 0x4
 FLAG_COUNTERS = 0x8
 FLAG_FLOAT_OUT = 0x10
+FLAG_OUT_FRAME = 0x20
 HIT_MISS = 0xFFFFFFFF
 
 SCENE_TERRAIN, SCENE_GLASS_CUBE, SCENE_REFRACTION, SCENE_SYNTHETIC = 0, 1, 2, 3
@@ -21,7 +22,7 @@ EXPORTS = [
     "vrt_upload_grid_device", "vrt_upload_atlas", "vrt_render", "vrt_render_to", "vrt_render_host", "vrt_tile_pixels",
     "vrt_framebuffer_device", "vrt_read_framebuffer", "vrt_read_debug_maps", "vrt_read_float_frame", "vrt_reset_counters",
     "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells",
-    "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_temporal_blend",
+    "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_device", "vrt_temporal_blend",
     "vrt_ipc_alloc_frame", "vrt_ipc_open", "vrt_ipc_close", "vrt_scene_fill", "vrt_noise_heightmap", "vrt_atlas_synthetic",
     "vrt_atlas_pack", "vrt_camera_invpv", "vrt_sun_dir",
 ]
@@ -114,6 +115,8 @@ def load_library():
         "vrt_device_alloc": (i32, [vp, C.c_size_t, C.POINTER(vp)]),
         "vrt_device_free": (i32, [vp, vp]),
         "vrt_synchronize": (i32, [vp, vp]),
+        "vrt_copy_to_host": (i32, [vp, vp, vp, C.c_size_t, vp]),
+        "vrt_copy_to_device": (i32, [vp, vp, vp, C.c_size_t, vp]),
         "vrt_temporal_blend": (i32, [vp, vp, vp, i64, f32, vp]),
         "vrt_ipc_alloc_frame": (i32, [vp, C.c_size_t, C.POINTER(vp), vp]),
         "vrt_ipc_open": (i32, [vp, vp, C.POINTER(vp)]),
@@ -337,6 +340,16 @@ class Context:
 
     def device_free(self, p):
         self._check(self.lib.vrt_device_free(self.h, p))
+
+    def copy_to_host(self, d_ptr, nbytes, stream=None):
+        """Device memory -> new numpy uint8 array."""
+        out = np.empty(nbytes, np.uint8)
+        self._check(self.lib.vrt_copy_to_host(self.h, _ptr(out), d_ptr, nbytes, stream))
+        return out
+
+    def copy_to_device(self, d_ptr, arr, stream=None):
+        a = np.ascontiguousarray(arr)
+        self._check(self.lib.vrt_copy_to_device(self.h, d_ptr, _ptr(a), a.nbytes, stream))
 
     def ipc_alloc_frame(self, nbytes):
         p = C.c_void_p()

@@ -39,10 +39,11 @@ __device__ __forceinline__ void render_one(const FrameArgs& f, int lx, int ly) {
   if (live) {
     const int px = f.p.tile_x0 + lx, py = frame_row(f.p, ly);
     PixelResult r = shade_pixel<Tracer, FLAT>(cx, px, py);
-    const size_t o = (size_t)ly * (size_t)f.p.tile_w + (size_t)lx;
+    const size_t o = (size_t)ly * (size_t)f.p.tile_w + (size_t)lx;                         // compact tile position
+    const size_t oc = (f.p.flags & VRT_FLAG_OUT_FRAME) ? (size_t)py * (size_t)f.p.width + (size_t)px : o;  // colour target
     uchar4 q;
     q.x = quantize_unorm8(r.rgba[0]); q.y = quantize_unorm8(r.rgba[1]); q.z = quantize_unorm8(r.rgba[2]); q.w = 255;
-    reinterpret_cast<uchar4*>(f.out_rgba8)[o] = q;
+    reinterpret_cast<uchar4*>(f.out_rgba8)[oc] = q;
     if (DEBUG) {
       if (f.out_f32) reinterpret_cast<float4*>(f.out_f32)[o] = make_float4(r.rgba[0], r.rgba[1], r.rgba[2], r.rgba[3]);
       if (f.out_hit) f.out_hit[o] = r.hit;

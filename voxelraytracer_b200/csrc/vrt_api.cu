@@ -222,6 +222,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   memset(&a, 0, sizeof(a));
   a.p = *p;
   a.grid = ctx->d_grid; a.cells = ctx->d_cells; a.atlas = ctx->d_atlas;
+  if (!d_out && (p->flags & VRT_FLAG_OUT_FRAME)) return fail(ctx, VRT_E_INVALID, "render: VRT_FLAG_OUT_FRAME needs vrt_render_to");
   if (!d_out) {
     if ((rc = ensure(ctx, &ctx->d_fb, &ctx->fb_bytes, (size_t)npix * 4))) return rc;
     d_out = ctx->d_fb;
@@ -400,6 +401,24 @@ int vrt_synchronize(vrt_ctx* ctx, void* stream) {
   if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_synchronize: NULL ctx");
   int rc = bind(ctx);
   if (rc) return rc;
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return VRT_OK;
+}
+
+int vrt_copy_to_host(vrt_ctx* ctx, void* host, const void* d_src, size_t bytes, void* stream) {
+  if (!ctx || !host || !d_src) return fail(ctx, VRT_E_INVALID, "vrt_copy_to_host: NULL argument");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(host, d_src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return VRT_OK;
+}
+
+int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes, void* stream) {
+  if (!ctx || !d_dst || !host) return fail(ctx, VRT_E_INVALID, "vrt_copy_to_device: NULL argument");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(d_dst, host, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
   CU(cudaStreamSynchronize((cudaStream_t)stream));
   return VRT_OK;
 }
