@@ -33,12 +33,32 @@ WORKLOADS = {
     "c3": ("refraction128", ["refraction_close"], 1920, 1080, 0),
     "c4": ("terrain128_glass", ["glass_wall", "terrain_inside"], 3840, 2160, 0),
     "c1": ("glass_cube32", ["start"], 400, 400, 1),
+    # C5: 64 poses on a circle of radius 600 around the 1024^3 chunk, looking inward; maxRayLength 2048
+    "c5": ("synthetic1024", ["orbit%d" % k for k in range(64)], 7680, 4320, 0),
+    "c5s": ("synthetic512", ["orbit%d" % k for k in range(64)], 3840, 2160, 0),   # half-size rehearsal of C5
 }
+MAX_LEN = {"c5": 2048.0, "c5s": 1024.0}
+
+
+def pose_of(workload, name):
+    """Named pose -> what common.make_params takes (orbit poses are generated)."""
+    if name.startswith("orbit"):
+        import common
+        scale = 0.5 if workload == "c5s" else 1.0
+        return common.orbit_pose(int(name[5:]), 64, 600.0 * scale, 250.0 * scale)
+    return name
+
+
+def mk(common, workload, W, H, sc, pose, flags):
+    return common.make_params(W, H, sc, pose_of(workload, pose), flags, max_len=MAX_LEN.get(workload))
+
 WORKLOAD_DESC = {
     "c2": "_TERRAIN 128^3 chunk, 1920x1080, primary + shadow rays, 256^2 atlas (BASELINE configs[1])",
     "c3": "_REFRACTION 128^3 chunk, 1920x1080, <= 4 reflection/refraction bounces (BASELINE configs[2])",
     "c4": "_TERRAIN + glass walls 128^3 chunk, 3840x2160 multi-bounce (BASELINE configs[3])",
     "c1": "_GLASS_CUBE + _HIGH_PERFORMANCE + _COLOR_ONLY 32^3, 400x400 (BASELINE configs[0])",
+    "c5": "synthetic 1024^3 procedural chunk, 7680x4320, 64 orbit poses, maxRayLength 2048 (BASELINE configs[4])",
+    "c5s": "synthetic 512^3 procedural chunk, 3840x2160, 64 orbit poses, maxRayLength 1024 (half-size rehearsal of configs[4])",
 }
 I_STEP = 16          # algorithmic thread-instructions per reference DDA step (SURVEY.md 8(d))
 # dram__bytes_read.sum + dram__bytes_write.sum per render_kernel launch from the committed `ncu --set full` capture (profiles/)
@@ -103,7 +123,7 @@ def run_reference(args):
     sc, poses, W, H, flags = WORKLOADS[args.workload]
     grid, n, atlas, ts = common.scene(sc)
     threads = os.cpu_count() or 1
-    frames = [common.make_params(W, H, sc, pose, flags) for pose in poses]
+    frames = [mk(common, args.workload, W, H, sc, pose, flags) for pose in poses]
     # Bounded sample: start from 1/4 of the scanlines and thin it until K + W steps fit in ~150 s on this box.
     every = 4
     dt, kind = cpu_reference_frame(common, frames[0], grid, atlas, strips(H, 12, every), threads)
@@ -231,10 +251,11 @@ def run_ours(args):
     npix = W * H
     frame_bytes = npix * 4
     if strong:      # ONE frame per step: every rank renders its 16-row bands of the same pose
-        full = [common.make_params(W, H, sc, poses[i % len(poses)], flags) for i in range(len(poses))]
+        full = [mk(common, args.workload, W, H, sc, poses[i % len(poses)], flags) for i in range(len(poses))]
         frames = [sharding.band_params(p, rank, world, BR) for p in full]
     else:           # one full frame per rank per step, each rank on its own pose sequence
-        frames = [common.make_params(W, H, sc, poses[(i + rank) % len(poses)], flags) for i in range(len(poses))]
+        frames = [mk(common, args.workload, W, H, sc, poses[(i + rank) % len(poses)], flags) for i in range(len(poses))]
+    frames = frames[:max(1, min(len(frames), args.steps))]      # only the poses the timed steps will cycle through
     my_pix = vrt.tile_pixels(frames[0])
 
     # reference-equivalent ray / step counts of what THIS rank renders (exact kernel's counters == oracle's, see tests)
@@ -455,9 +476,9 @@ def run_ours(args):
             "metric": "Mrays/s at 1080p terrain scene" if args.workload == "c2" else "Mrays/s", "value": rays_all / t_step_total / 1e6,
             "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_step_total / args.steps,
             "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_DESC[args.workload], "poses": poses, "frame": [W, H], "traversal": args.mode, "sharding": shard,
+            "config": {"workload": WORKLOAD_DESC[args.workload], "poses": poses if len(poses) <= 8 else "%d orbit poses" % len(poses), "frame": [W, H], "traversal": args.mode, "sharding": shard,
                        "l2": "flushed: 256 MiB fill before every timed step window (the fill itself is outside the window)",
-                       "maxRayLength": 100.0},
+                       "maxRayLength": MAX_LEN.get(args.workload, 100.0)},
             "frames_per_s": frames_total / t_step_total,
             "kernel_ms_per_launch": 1e3 * t_kernel_max / args.steps,
             "rays_per_frame": rays_all / frames_total, "ref_steps_per_frame": steps_all / frames_total,

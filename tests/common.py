@@ -188,8 +188,9 @@ def scene(name):
         r = (vrt.scene_fill("refraction", 128), 128, vrt.atlas_synthetic(128), 128)
     elif name == "refraction32":
         r = (vrt.scene_fill("refraction", 32), 32, vrt.atlas_synthetic(16), 16)
-    elif name == "synthetic256":
-        r = (vrt.scene_fill("synthetic", 256, seed=7), 256, vrt.atlas_synthetic(128), 128)
+    elif name.startswith("synthetic"):  # C5 family: synthetic256 / synthetic512 / synthetic1024
+        sz = int(name[len("synthetic"):])
+        r = (vrt.scene_fill("synthetic", sz, seed=7), sz, vrt.atlas_synthetic(128), 128)
     else:
         raise KeyError(name)
     _scene_cache[name] = r
@@ -209,7 +210,16 @@ POSES = {
 }
 
 
-def make_params(width, height, scene_name, pose, flags=0, aspect=None, noise=(0.0, 0.0, 0.0), time=1.0, time_of_day=0.0):
+def orbit_pose(k, count=64, radius=600.0, height=250.0):
+    """Pose k of `count` on a circle around the chunk centre, looking at the centre."""
+    a = 2.0 * np.pi * k / count
+    pos = np.array([radius * np.cos(a), height, radius * np.sin(a)])
+    f = -pos / np.linalg.norm(pos)
+    # forward = Ry(ry) Rx(rx) (0,0,-1) = (-cos rx sin ry, sin rx, -cos rx cos ry)  (camera_invpv's view = Rx(-rx) Ry(-ry) T(-pos))
+    return (tuple(float(x) for x in pos), (float(np.arcsin(f[1])), float(np.arctan2(-f[0], -f[2])), 0.0))
+
+
+def make_params(width, height, scene_name, pose, flags=0, aspect=None, noise=(0.0, 0.0, 0.0), time=1.0, time_of_day=0.0, max_len=None):
     grid, n, atlas, ts = scene(scene_name)
     p = vrt.default_params(width, height, n)
     pos, rot = POSES[pose] if isinstance(pose, str) else pose
@@ -224,6 +234,8 @@ def make_params(width, height, scene_name, pose, flags=0, aspect=None, noise=(0.
     p.flags = flags
     p.rayNoise, p.reflectionNoise, p.refractionNoise = noise
     p.time = time
+    if max_len is not None:
+        p.maxRayLength = float(max_len)
     return p
 
 
