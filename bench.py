@@ -79,6 +79,7 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: one full frame per GPU per step (pose batch); strong: ONE frame per step, 16-row bands dealt round-robin")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
     return ap.parse_args()
 
 
@@ -245,6 +246,8 @@ def run_ours(args):
     ctx.upload_atlas(atlas, ts)
     if args.mode == "exact":
         flags |= vrt.FLAG_EXACT
+    if args.persistent:
+        flags |= vrt.FLAG_PERSISTENT
     strong = args.scaling == "strong" and world > 1
     gather = args.gather if world > 1 else "none"
     BR = 16

@@ -48,6 +48,9 @@ enum {
                                      several GPUs render disjoint tiles straight into one frame (e.g. rank 0's, mapped over
                                      NVLink with vrt_ipc_open): the gather is the kernel's own stores. */
 
+#define VRT_FLAG_PERSISTENT 0x40u /* tuning: persistent-warp launch (resident CTAs pull 8x4 patches from an atomic ticket)
+                                     instead of one CTA per 16x8 patch; same pixels.  Ignored with EXACT / debug flags. */
+
 #define VRT_HIT_MISS 0xFFFFFFFFu
 
 /* Per-frame inputs == the uniforms AppScene::Render() sets (src/main.cpp:333-348; declared at

@@ -168,3 +168,14 @@ def test_out_frame_flag_writes_bands_in_place(ctx):
     with pytest.raises(vrt.VrtError):
         q = p.copy(); q.flags |= vrt.FLAG_OUT_FRAME
         ctx.render(q)                                 # needs vrt_render_to
+
+
+def test_persistent_launch_writes_the_same_pixels(ctx):
+    for sc, pose, fl, W, H in (("terrain128", "terrain_low", 0, 1001, 563), ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY, 400, 400)):
+        grid, n, atlas, ts = upload(ctx, sc)
+        p = make_params(W, H, sc, pose, fl)
+        a = gpu_render(ctx, p, flags_extra=0).rgba8
+        b = gpu_render(ctx, p, flags_extra=vrt.FLAG_PERSISTENT).rgba8
+        assert np.array_equal(a, b)
+        q = p.copy(); q.tile_x0, q.tile_y0, q.tile_w, q.tile_h = 37, 11, 300, 201
+        assert np.array_equal(gpu_render(ctx, q, flags_extra=0).rgba8, gpu_render(ctx, q, flags_extra=vrt.FLAG_PERSISTENT).rgba8)

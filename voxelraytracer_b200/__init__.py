@@ -15,6 +15,7 @@ from .api import (  # noqa: F401
     FLAG_EXACT,
     FLAG_FLOAT_OUT,
     FLAG_OUT_FRAME,
+    FLAG_PERSISTENT,
     HIT_MISS,
     Context,
     Counters,

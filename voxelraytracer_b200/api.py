@@ -12,6 +12,7 @@ FLAG_EXACT = 0x4
 FLAG_COUNTERS = 0x8
 FLAG_FLOAT_OUT = 0x10
 FLAG_OUT_FRAME = 0x20
+FLAG_PERSISTENT = 0x40
 HIT_MISS = 0xFFFFFFFF
 
 SCENE_TERRAIN, SCENE_GLASS_CUBE, SCENE_REFRACTION, SCENE_SYNTHETIC = 0, 1, 2, 3

@@ -70,6 +70,43 @@ __global__ void VRT_BOUNDS render_kernel(const __grid_constant__ FrameArgs f) {
   render_one<Tracer, FLAT, DEBUG>(f, lx, ly);
 }
 
+// Persistent variant: 148 x VRT_MIN_BLOCKS resident CTAs; every WARP pulls 8x4-pixel patches from an atomic counter
+// until the frame is done (warp-level queue: lane 0 takes the ticket, __shfl_sync broadcasts it).  Patches are
+// numbered in 2x2 groups so that tickets handed out together are neighbours on screen.
+template <class Tracer, bool FLAT, bool DEBUG>
+__global__ void VRT_BOUNDS render_kernel_persistent(const __grid_constant__ FrameArgs f, unsigned int* __restrict__ ticket, int patches_x,
+                                                      int patches_y) {
+  const int lane = threadIdx.x & 31;
+  const int gx = (patches_x + 1) >> 1;
+  const unsigned total = (unsigned)gx * (unsigned)((patches_y + 1) >> 1) * 4u;
+  for (;;) {
+    unsigned t = 0;
+    if (lane == 0) t = atomicAdd(ticket, 1u);
+    t = __shfl_sync(0xFFFFFFFFu, t, 0);
+    if (t >= total) break;
+    const unsigned g = t >> 2, q = t & 3u;
+    const int ptx = (int)(g % (unsigned)gx) * 2 + (int)(q & 1u), pty = (int)(g / (unsigned)gx) * 2 + (int)(q >> 1);
+    if (ptx >= patches_x || pty >= patches_y) continue;
+    render_one<Tracer, FLAT, DEBUG>(f, ptx * kWarpW + (lane & (kWarpW - 1)), pty * kWarpH + (lane / kWarpW));
+  }
+}
+
+template <class Tracer, bool FLAT, bool DEBUG>
+static cudaError_t launch_variant_persistent(const FrameArgs& a, unsigned int* ticket, int num_sms, cudaStream_t s) {
+  const int px = (a.p.tile_w + kWarpW - 1) / kWarpW, py = (a.rows_local + kWarpH - 1) / kWarpH;
+  if (px == 0 || py == 0) return cudaSuccess;
+  cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned int), s);
+  if (e != cudaSuccess) return e;
+  const int per_sm = VRT_MIN_BLOCKS > 0 ? VRT_MIN_BLOCKS : 8;
+  render_kernel_persistent<Tracer, FLAT, DEBUG><<<num_sms * per_sm, kThreads, 0, s>>>(a, ticket, px, py);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_render_persistent(const FrameArgs& a, bool flat, unsigned int* ticket, int num_sms, cudaStream_t s) {
+  if (flat) return launch_variant_persistent<FastTracer<true, false>, true, false>(a, ticket, num_sms, s);
+  return launch_variant_persistent<FastTracer<false, false>, false, false>(a, ticket, num_sms, s);
+}
+
 template <class Tracer, bool FLAT, bool DEBUG>
 static cudaError_t launch_variant(const FrameArgs& a, cudaStream_t s) {
   dim3 grid((unsigned)((a.p.tile_w + kCtaW - 1) / kCtaW), (unsigned)((a.rows_local + kCtaH - 1) / kCtaH));

@@ -29,6 +29,8 @@ VRT_HD void vset(V3& v, int a, float s) { if (a == 0) v.x = s; else if (a == 1) 
 // GLSL built-ins with the pins of SURVEY.md 8(a'): dot = ((xx + yy) + zz); normalize = v / sqrt(dot) (G7)
 VRT_HD float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 VRT_HD V3 normalize3(V3 v) { float l = sqrtf(dot3(v, v)); return mk3(v.x / l, v.y / l, v.z / l); }
+// fast-traversal variant: one IEEE reciprocal and three multiplies (last-ulp differences from the pinned form)
+VRT_HD V3 normalize3_lean(V3 v) { float il = 1.0f / sqrtf(dot3(v, v)); return mk3(v.x * il, v.y * il, v.z * il); }
 VRT_HD float sign1(float x) { return x > 0.0f ? 1.0f : (x < 0.0f ? -1.0f : 0.0f); }
 VRT_HD float gmin(float x, float y) { return y < x ? y : x; }
 VRT_HD float gmax(float x, float y) { return x < y ? y : x; }
@@ -75,7 +77,7 @@ VRT_HD V3 randomize_direction(V3 dir, V3 pos, float randomness, float seed) {
 // literal form is the sign of a zero component, which the fast traversal never looks at (the exact one does, so it
 // keeps the literal form).
 VRT_HD V3 randomize_direction_lean(V3 dir, V3 pos, float randomness, float seed) {
-  if (randomness == 0.0f) return normalize3(mk3(dir.x + 0.0f, dir.y + 0.0f, dir.z + 0.0f));
+  if (randomness == 0.0f) return normalize3_lean(dir);
   return randomize_direction(dir, pos, randomness, seed);
 }
 

@@ -11,6 +11,7 @@ namespace vrt {
 // the exact traversal instantiates LEAN = false and stays a literal replay.
 template <bool FLAT, bool COUNT, bool LEAN = false>
 struct PixelCtx {
+  static constexpr bool kLean = LEAN;
   const FrameArgs& f;
   PixelCounters cnt;
   VRT_HD explicit PixelCtx(const FrameArgs& fa) : f(fa) { if (COUNT) cnt.clear(); }
@@ -53,7 +54,12 @@ struct PixelCtx {
     j = j < 0 ? 0 : (j > n - 1 ? n - 1 : j);
 #if defined(__CUDA_ARCH__)
     uchar4 t = __ldg(reinterpret_cast<const uchar4*>(f.atlas) + ((size_t)j * n + i));
-    c[0] = (float)t.x / 255.0f; c[1] = (float)t.y / 255.0f; c[2] = (float)t.z / 255.0f; c[3] = (float)t.w / 255.0f;
+    if (LEAN) {   // x * (1/255) instead of x / 255: within 1 ulp, alpha 255 still maps to exactly 1.0f
+      const float k = 1.0f / 255.0f;
+      c[0] = (float)t.x * k; c[1] = (float)t.y * k; c[2] = (float)t.z * k; c[3] = t.w == 255 ? 1.0f : (float)t.w * k;
+    } else {
+      c[0] = (float)t.x / 255.0f; c[1] = (float)t.y / 255.0f; c[2] = (float)t.z / 255.0f; c[3] = (float)t.w / 255.0f;
+    }
 #else
     const uint8_t* t = f.atlas + ((size_t)j * n + i) * 4;
     for (int k = 0; k < 4; k++) c[k] = (float)t[k] / 255.0f;
@@ -98,7 +104,7 @@ struct PixelCtx {
     V3 n = normal_of(h);
     float n_out = refractivity(voxel_at(h.point.x + n.x * 0.5f, h.point.y + n.y * 0.5f, h.point.z + n.z * 0.5f, nullptr));
     float n_in = refractivity(voxel_at(h.point.x - n.x * 0.5f, h.point.y - n.y * 0.5f, h.point.z - n.z * 0.5f, nullptr));
-    V3 I = normalize3(r.dir);
+    V3 I = LEAN ? normalize3_lean(r.dir) : normalize3(r.dir);
     float eta = n_out / n_in;
     float d = dot3(n, I);
     float k = 1.0f - eta * eta * (1.0f - d * d);
@@ -133,7 +139,7 @@ struct PixelCtx {
 
   // GetSkyboxColor (voxel.glsl:386-393) with pin G2
   VRT_HD V3 sky(const Ray& r, V3 color) const {
-    V3 u = normalize3(r.dir);
+    V3 u = LEAN ? normalize3_lean(r.dir) : normalize3(r.dir);
     float d = dot3(f.sun_unit, u);
     float sun = d < 0.0f ? 0.0f : 10.0f * pow_pos(d, 400.0f);
     float grad = (u.y + 1.0f) * 0.5f;
@@ -187,6 +193,8 @@ template <class Tracer, bool FLAT>
 VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
   const vrt_params& p = cx.f.p;
   const float* m = p.invPV;
+  // kept as IEEE divisions in both traversals: a 1-ulp error in the NDC coordinate measurably raises the number of
+  // grazing-ray mismatches against the oracle (tools/parity_report.py), unlike the reciprocals further down
   float nx = ((float)px + 0.5f) / (float)p.width * 2.0f - 1.0f;
   float ny = ((float)py + 0.5f) / (float)p.height * 2.0f - 1.0f;
   float nr[4], fr[4];
@@ -196,15 +204,23 @@ VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
     nr[i] = (xy + m[8 + i] * -1.0f) + m[12 + i] * 1.0f;
     fr[i] = (xy + m[8 + i] * 1.0f) + m[12 + i] * 1.0f;
   }
-  V3 vnear = mk3(nr[0] / nr[3], nr[1] / nr[3], nr[2] / nr[3]);
-  V3 vdir = mk3(fr[0] / fr[3] - vnear.x, fr[1] / fr[3] - vnear.y, fr[2] / fr[3] - vnear.z);
+  V3 vnear, vdir;
+  if (Tracer::Ctx::kLean) {   // reciprocal-multiply instead of three IEEE divisions each
+    const float iw = 1.0f / nr[3], jw = 1.0f / fr[3];
+    vnear = mk3(nr[0] * iw, nr[1] * iw, nr[2] * iw);
+    vdir = mk3(fr[0] * jw - vnear.x, fr[1] * jw - vnear.y, fr[2] * jw - vnear.z);
+  } else {
+    vnear = mk3(nr[0] / nr[3], nr[1] / nr[3], nr[2] / nr[3]);
+    vdir = mk3(fr[0] / fr[3] - vnear.x, fr[1] / fr[3] - vnear.y, fr[2] / fr[3] - vnear.z);
+  }
 
   constexpr int kStack = 8;  // maxReflections + maxTransparencies + 1 <= 8 (checked by the API)
   Ray stack[kStack];         // only bounce rays ever live here; the primary ray stays in registers
   float half = cx.f.fsize * 0.5f;
   Ray r;
   r.pos = mk3(vnear.x + half, vnear.y + half, vnear.z + half);
-  r.dir = cx.jitter(normalize3(vdir), vnear, p.rayNoise);
+  // the shader normalises twice (voxel.glsl:430 and :139); with zero noise the lean path does it once
+  r.dir = (Tracer::Ctx::kLean && p.rayNoise == 0.0f) ? normalize3_lean(vdir) : cx.jitter(normalize3(vdir), vnear, p.rayNoise);
   r.len = 0.0f; r.energy = 1.0f; r.medium = 0; r.nrefl = 0; r.ntrans = 0; r.face_axis = -1; r.face_nsign = 0.0f;
   int n = 0, popped = 0;
   V3 color = mk3(0.0f, 0.0f, 0.0f);

@@ -241,7 +241,11 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   a.rows_local = (int)(npix / p->tile_w);
   finish_frame_args(a);
   CU(cudaEventRecord(ctx->ev0, s));
-  CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, s));
+  if ((p->flags & VRT_FLAG_PERSISTENT) && !debug && !(p->flags & VRT_FLAG_EXACT)) {
+    CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, (unsigned int*)(ctx->d_stats + 4), ctx->num_sms, s));
+  } else {
+    CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, s));
+  }
   CU(cudaEventRecord(ctx->ev1, s));
   ctx->launches += 1;
   ctx->timed = true;
