@@ -79,6 +79,7 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: one full frame per GPU per step (pose batch); strong: ONE frame per step, 16-row bands dealt round-robin")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--octants", type=int, default=1, choices=[0, 1], help="VRT_OPT_OCTANT_FIELDS (tuning comparison; 1 = default)")
     ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
     return ap.parse_args()
 
@@ -242,7 +243,10 @@ def run_ours(args):
     sc, poses, W, H, flags = WORKLOADS[args.workload]
     grid, n, atlas, ts = common.scene(sc)
     ctx = vrt.Context(local)
+    ctx.set_option(vrt.OPT_OCTANT_FIELDS, args.octants)
+    t_up0 = time.perf_counter()
     ctx.upload_grid(grid, n)
+    t_upload = time.perf_counter() - t_up0
     ctx.upload_atlas(atlas, ts)
     if args.mode == "exact":
         flags |= vrt.FLAG_EXACT
@@ -497,6 +501,7 @@ def run_ours(args):
                     "call": "vrt_render_host (params by value, RGBA8 pixels copied to pinned host memory, synchronised), per rank"},
             "gpu_launches": int(launches_timed),      # render_kernel launches of rank 0 inside the timed region (one per step)
             "gather_check": gather_check,
+            "upload_grid_s": t_upload, "radius_fields": "8 direction-octant fields" if args.octants else "1 isotropic field",
             "pipelined": None if not t_pipeline else {"value": rays_all / t_pipeline / 1e6, "unit": "Mrays/s",
                                                        "note": "same steps back to back, no L2 fills: step i+1's render overlaps step i's gather/signal"},
             "clocks": clocks,

@@ -145,15 +145,23 @@ int vrt_last_render_ms(vrt_ctx* ctx, float* ms);
 int64_t vrt_kernel_launches(const vrt_ctx* ctx);
 
 /* ---- repacked grid inspection (tests) ----
- * The upload repacks the chunk into traversal cells: a (size+2)^3 array of uint16 with a one-cell border,
- * cell = (emptyRadius << 8) | voxelByte, emptyRadius = Chebyshev distance to the nearest occupied voxel or
- * border cell (0 for occupied and border cells), capped at radius_cap.  Index (x+1) + (y+1)*pitch + (z+1)*pitch^2. */
+ * The upload repacks the chunk into traversal cells: arrays of (size+2)^3 uint16 with a one-cell border of 0,
+ * cell = (emptyRadius << 8) | voxelByte, index (x+1) + (y+1)*pitch + (z+1)*pitch^2, emptyRadius capped at radius_cap
+ * and 0 for occupied and border cells.
+ *   octants == 8 (default): eight arrays back to back, array o = (dx < 0) | (dy < 0) << 1 | (dz < 0) << 2 serves rays of
+ *     that direction octant; emptyRadius = edge of the largest empty in-chunk box that starts at the cell and extends
+ *     FORWARD along the octant's signs (forward Chebyshev distance to the nearest occupied or border cell).
+ *   octants == 1: one array; emptyRadius = Chebyshev distance to the nearest occupied or border cell in any direction. */
 typedef struct vrt_grid_info {
-  int32_t size, pitch, radius_cap, reserved;
+  int32_t size, pitch, radius_cap, octants;
   int64_t cells_total, voxels_occupied;
 } vrt_grid_info;
 int vrt_grid_info_get(vrt_ctx* ctx, vrt_grid_info* out);
-int vrt_read_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count); /* count must be (size+2)^3 */
+int vrt_read_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count); /* count must be cells_total */
+
+/* Tuning options; take effect at the next vrt_upload_grid. */
+enum { VRT_OPT_OCTANT_FIELDS = 1 /* 1 (default) = eight direction-octant radius fields, 0 = one isotropic field */ };
+int vrt_set_option(vrt_ctx* ctx, int option, int value);
 
 /* ---- memory helpers for callers without a CUDA toolchain (ctypes, cgo ...) ---- */
 int vrt_host_alloc(vrt_ctx* ctx, size_t bytes, void** out);   /* pinned host memory */

@@ -130,16 +130,28 @@ def ref_render(p, grid, atlas, nthreads=NCPU):
 _cells_cache = {}
 
 
-def hostsim_cells(grid, size):
-    key = (hash(grid.tobytes()), size)
+OCTANTS = int(os.environ.get("VRT_TEST_OCTANTS", "1"))   # what the product builds by default (vrt_set_option can change it)
+
+
+def radius_cap(size):
+    return 255 if size <= 256 else 96
+
+
+def hostsim_cells(grid, size, octants=None):
+    octants = OCTANTS if octants is None else octants
+    key = (hash(grid.tobytes()), size, octants)
     if key not in _cells_cache:
-        cells = np.zeros((size + 2) ** 3, np.uint16)
-        assert hostsim_lib().hostsim_build_cells(_p(grid), size, _p(cells)) == 0
+        if octants:
+            cells = np.zeros(8 * (size + 2) ** 3, np.uint16)
+            assert hostsim_lib().hostsim_build_cells_oct(_p(grid), size, radius_cap(size), _p(cells)) == 0
+        else:
+            cells = np.zeros((size + 2) ** 3, np.uint16)
+            assert hostsim_lib().hostsim_build_cells(_p(grid), size, _p(cells)) == 0
         _cells_cache[key] = cells
     return _cells_cache[key]
 
 
-def hostsim_render(p, grid, atlas, mode, nthreads=NCPU):
+def hostsim_render(p, grid, atlas, mode, nthreads=NCPU, octants=None):
     """mode 0 = exact tracer, 1 = fast tracer (the product's device headers compiled for the host)."""
     n = vrt.tile_pixels(p)
     f32 = np.zeros((n, 4), np.float32)
@@ -147,8 +159,9 @@ def hostsim_render(p, grid, atlas, mode, nthreads=NCPU):
     hit = np.zeros(n, np.uint32)
     nb = np.zeros(n, np.uint8)
     cnt = (C.c_uint64 * 8)()
-    cells = hostsim_cells(grid, p.size)
-    rc = hostsim_lib().hostsim_render(C.byref(p), _p(grid), _p(cells), _p(atlas), mode, _p(f32), _p(q), _p(hit), _p(nb), cnt, nthreads)
+    octants = OCTANTS if octants is None else octants
+    cells = hostsim_cells(grid, p.size, octants)
+    rc = hostsim_lib().hostsim_render(C.byref(p), _p(grid), _p(cells), octants, _p(atlas), mode, _p(f32), _p(q), _p(hit), _p(nb), cnt, nthreads)
     assert rc == 0, "hostsim_render failed"
     names = ("primary_rays", "secondary_rays", "shadow_rays", "march_steps", "shadow_steps", "actual_steps", "hits", "tie_index3")
     return Frame(f32=f32, rgba8=q, hit=hit, bounces=nb, counters=dict(zip(names, [int(x) for x in cnt])))

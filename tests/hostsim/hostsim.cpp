@@ -65,6 +65,51 @@ int hostsim_build_cells(const uint8_t* grid, int n, uint16_t* cells) {
   return 0;
 }
 
+// Octant fields: 8 arrays like the one above, array o for rays with direction signs s = (o&1 ? -1 : +1, o&2 ? -1 : +1,
+// o&4 ? -1 : +1).  High byte = largest k such that the forward box {c + s*d : d in [0,k)^3} is empty and inside the
+// chunk, capped at `cap` (0 for occupied cells) == forward Chebyshev distance to the nearest occupied-or-border cell.
+// Computed here with the maximal-cube recurrence D(c) = 1 + min over the 7 forward neighbours, an algorithm that
+// shares nothing with the separable one-sided scans of repack.cu.
+int hostsim_build_cells_oct(const uint8_t* grid, int n, int cap, uint16_t* cells) {
+  const int P = n + 2;
+  const size_t P3 = (size_t)P * P * P;
+  std::memset(cells, 0, 8 * P3 * sizeof(uint16_t));
+  std::vector<uint8_t> D((size_t)n * n * n);
+  auto at = [n](int x, int y, int z) { return (size_t)x + (size_t)y * n + (size_t)z * n * n; };
+  for (int o = 0; o < 8; o++) {
+    const int sx = o & 1 ? -1 : 1, sy = o & 2 ? -1 : 1, sz = o & 4 ? -1 : 1;
+    auto get = [&](int x, int y, int z) -> int {
+      if (x < 0 || y < 0 || z < 0 || x >= n || y >= n || z >= n) return 0;  // border cells are obstacles
+      return D[at(x, y, z)];
+    };
+    for (int kz = 0; kz < n; kz++)
+      for (int ky = 0; ky < n; ky++)
+        for (int kx = 0; kx < n; kx++) {
+          // visit in the order in which all forward neighbours are already done
+          const int x = sx > 0 ? n - 1 - kx : kx, y = sy > 0 ? n - 1 - ky : ky, z = sz > 0 ? n - 1 - kz : kz;
+          int d = 0;
+          if (!grid[at(x, y, z)]) {
+            int m = 255;
+            for (int e = 1; e < 8; e++) {
+              int v = get(x + (e & 1 ? sx : 0), y + (e & 2 ? sy : 0), z + (e & 4 ? sz : 0));
+              if (v < m) m = v;
+            }
+            d = 1 + m;
+            if (d > cap) d = cap;
+          }
+          D[at(x, y, z)] = (uint8_t)d;
+        }
+    uint16_t* out = cells + (size_t)o * P3;
+    for (int z = 0; z < n; z++)
+      for (int y = 0; y < n; y++)
+        for (int x = 0; x < n; x++) {
+          uint8_t v = grid[at(x, y, z)];
+          out[(size_t)(x + 1) + (size_t)(y + 1) * P + (size_t)(z + 1) * P * P] = (uint16_t)(((v ? 0 : D[at(x, y, z)]) << 8) | v);
+        }
+  }
+  return 0;
+}
+
 }  // extern "C"
 
 template <class Tracer, bool FLAT>
@@ -98,7 +143,8 @@ static void render_rows(const FrameArgs& f, std::atomic<int>& next, float* out_f
 extern "C" {
 
 // mode: 0 = exact tracer, 1 = fast tracer (cells required).  counters: CNT_N (8) uint64, optional.
-int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cells, const uint8_t* atlas, int mode, float* out_f32,
+// octants: 0 = `cells` is one isotropic array, 1 = eight octant arrays (hostsim_build_cells_oct).
+int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cells, int octants, const uint8_t* atlas, int mode, float* out_f32,
                    uint8_t* out_rgba8, uint32_t* out_hit, uint8_t* out_bounces, uint64_t* counters, int nthreads) {
   if (!p || !grid) return -1;
   if (mode == 1 && !cells) return -1;
@@ -106,6 +152,7 @@ int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cel
   std::memset(&f, 0, sizeof(f));
   f.p = *p;
   f.grid = grid; f.cells = cells; f.atlas = atlas;
+  f.oct_stride = octants ? (size_t)(p->size + 2) * (p->size + 2) * (p->size + 2) : 0;
   f.rows_local = (int)(vrt_tile_pixels(p) / p->tile_w);
   if (!finish_frame_args(f)) return -1;
   bool flat = (p->flags & VRT_FLAG_COLOR_ONLY) != 0;

@@ -76,12 +76,34 @@ def test_plain_render_equals_debug_render(ctx):
 
 
 def test_repack_matches_host_statement(ctx):
-    for sc in ("glass_cube32", "terrain32", "terrain128_glass", "refraction128"):
-        grid, n, atlas, ts = scene(sc)
-        ctx.upload_grid(grid, n)
-        assert np.array_equal(ctx.read_cells(n), hostsim_cells(grid, n)), sc
-        info = ctx.grid_info()
-        assert info.size == n and info.pitch == n + 2 and info.voxels_occupied == int((grid != 0).sum())
+    """Device repack (separable one-sided scans) == the host statement (maximal-cube recurrence), both layouts."""
+    try:
+        for octants in (1, 0):
+            ctx.set_option(vrt.OPT_OCTANT_FIELDS, octants)
+            for sc in ("glass_cube32", "terrain32", "terrain128_glass", "refraction128"):
+                grid, n, atlas, ts = scene(sc)
+                ctx.upload_grid(grid, n)
+                assert np.array_equal(ctx.read_cells(), hostsim_cells(grid, n, octants)), (sc, octants)
+                info = ctx.grid_info()
+                assert info.size == n and info.pitch == n + 2 and info.voxels_occupied == int((grid != 0).sum())
+                assert info.octants == (8 if octants else 1) and info.cells_total == (8 if octants else 1) * (n + 2) ** 3
+    finally:
+        ctx.set_option(vrt.OPT_OCTANT_FIELDS, 1)
+
+
+def test_isotropic_field_option_renders_within_caps(ctx):
+    """VRT_OPT_OCTANT_FIELDS = 0 (one isotropic radius field) is still a valid traversal; device == host simulation."""
+    try:
+        ctx.set_option(vrt.OPT_OCTANT_FIELDS, 0)
+        grid, n, atlas, ts = upload(ctx, "terrain128_glass")
+        p = make_params(480, 270, "terrain128_glass", "glass_wall")
+        o = oracle_render(p, grid, atlas)
+        g = gpu_render(ctx, p)
+        assert int(((g.hit != o.hit) | (g.bounces != o.bounces)).sum()) <= max(2, int(1e-4 * 480 * 270))
+        h = hostsim_render(p, grid, atlas, 1, octants=0)
+        assert np.array_equal(g.hit, h.hit) and g.counters["actual_steps"] == h.counters["actual_steps"]
+    finally:
+        ctx.set_option(vrt.OPT_OCTANT_FIELDS, 1)
 
 
 def test_c2_full_size_1080p(ctx):

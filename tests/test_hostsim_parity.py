@@ -71,18 +71,30 @@ def test_fast_tracer_custom_limits_and_ray_length():
 
 
 def test_cells_radius_is_exact_chebyshev_distance():
+    """Both layouts against the brute-force definition: isotropic Chebyshev distance, and per octant the forward
+    Chebyshev distance (obstacles = occupied voxels and border cells, restricted to the closed forward octant)."""
     rng = np.random.default_rng(3)
     n = 16
     g = (rng.random(n ** 3) < 0.01).astype(np.uint8) * rng.integers(1, 4, n ** 3).astype(np.uint8)
-    cells = hostsim_cells(g, n).reshape(n + 2, n + 2, n + 2)
     occ = np.ones((n + 2,) * 3, bool)          # border counts as an obstacle
     occ[1:-1, 1:-1, 1:-1] = g.reshape(n, n, n) != 0
     zz, yy, xx = np.nonzero(occ)
     pts = np.stack([zz, yy, xx], 1)
+    iso = hostsim_cells(g, n, 0).reshape(n + 2, n + 2, n + 2)
+    octs = hostsim_cells(g, n, 1).reshape(8, n + 2, n + 2, n + 2)
     for _ in range(300):
-        c = rng.integers(1, n + 1, 3)
+        c = rng.integers(1, n + 1, 3)          # (z, y, x), padded coordinates
+        byte = g.reshape(n, n, n)[c[0] - 1, c[1] - 1, c[2] - 1]
         d = np.abs(pts - c).max(axis=1).min()
-        v = int(cells[c[0], c[1], c[2]])
-        assert (v >> 8) == min(d, 255)
-        assert (v & 0xFF) == g.reshape(n, n, n)[c[0] - 1, c[1] - 1, c[2] - 1]
-    assert (cells[0] == 0).all() and (cells[:, 0] == 0).all() and (cells[:, :, -1] == 0).all()
+        v = int(iso[c[0], c[1], c[2]])
+        assert (v >> 8) == min(d, 255) and (v & 0xFF) == byte
+        for o in range(8):
+            sgn = np.array([-1 if o & 4 else 1, -1 if o & 2 else 1, -1 if o & 1 else 1])   # (z, y, x)
+            rel = (pts - c) * sgn
+            fwd = (rel >= 0).all(axis=1)
+            df = rel[fwd].max(axis=1).min()
+            w = int(octs[o, c[0], c[1], c[2]])
+            assert (w >> 8) == min(df, 255) and (w & 0xFF) == byte, (o, c, w >> 8, df)
+            assert (w >> 8) >= (v >> 8)        # a forward box is never smaller than the centred cube
+    for cells in (iso, octs[0], octs[7]):
+        assert (cells[0] == 0).all() and (cells[:, 0] == 0).all() and (cells[:, :, -1] == 0).all()

@@ -17,6 +17,7 @@ from .api import (  # noqa: F401
     FLAG_OUT_FRAME,
     FLAG_PERSISTENT,
     HIT_MISS,
+    OPT_OCTANT_FIELDS,
     Context,
     Counters,
     GridInfo,

@@ -13,6 +13,7 @@ FLAG_COUNTERS = 0x8
 FLAG_FLOAT_OUT = 0x10
 FLAG_OUT_FRAME = 0x20
 FLAG_PERSISTENT = 0x40
+OPT_OCTANT_FIELDS = 1
 HIT_MISS = 0xFFFFFFFF
 
 SCENE_TERRAIN, SCENE_GLASS_CUBE, SCENE_REFRACTION, SCENE_SYNTHETIC = 0, 1, 2, 3
@@ -22,7 +23,7 @@ EXPORTS = [
     "vrt_default_params", "vrt_abi_version", "vrt_create", "vrt_destroy", "vrt_last_error", "vrt_upload_grid",
     "vrt_upload_grid_device", "vrt_upload_atlas", "vrt_render", "vrt_render_to", "vrt_render_host", "vrt_tile_pixels",
     "vrt_framebuffer_device", "vrt_read_framebuffer", "vrt_read_debug_maps", "vrt_read_float_frame", "vrt_reset_counters",
-    "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells",
+    "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells", "vrt_set_option",
     "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_device", "vrt_temporal_blend",
     "vrt_ipc_alloc_frame", "vrt_ipc_open", "vrt_ipc_close", "vrt_scene_fill", "vrt_noise_heightmap", "vrt_atlas_synthetic",
     "vrt_atlas_pack", "vrt_camera_invpv", "vrt_sun_dir",
@@ -65,7 +66,7 @@ class Counters(C.Structure):
 
 
 class GridInfo(C.Structure):
-    _fields_ = [("size", C.c_int32), ("pitch", C.c_int32), ("radius_cap", C.c_int32), ("reserved", C.c_int32),
+    _fields_ = [("size", C.c_int32), ("pitch", C.c_int32), ("radius_cap", C.c_int32), ("octants", C.c_int32),
                 ("cells_total", C.c_int64), ("voxels_occupied", C.c_int64)]
 
 
@@ -111,6 +112,7 @@ def load_library():
         "vrt_kernel_launches": (i64, [vp]),
         "vrt_grid_info_get": (i32, [vp, C.POINTER(GridInfo)]),
         "vrt_read_cells": (i32, [vp, vp, C.c_size_t]),
+        "vrt_set_option": (i32, [vp, i32, i32]),
         "vrt_host_alloc": (i32, [vp, C.c_size_t, C.POINTER(vp)]),
         "vrt_host_free": (i32, [vp, vp]),
         "vrt_device_alloc": (i32, [vp, C.c_size_t, C.POINTER(vp)]),
@@ -314,8 +316,11 @@ class Context:
         self._check(self.lib.vrt_grid_info_get(self.h, C.byref(g)))
         return g
 
-    def read_cells(self, size):
-        out = np.zeros((size + 2) ** 3, np.uint16)
+    def set_option(self, option, value):
+        self._check(self.lib.vrt_set_option(self.h, option, value))
+
+    def read_cells(self, size=None):
+        out = np.zeros(self.grid_info().cells_total, np.uint16)
         self._check(self.lib.vrt_read_cells(self.h, _ptr(out), out.size))
         return out
 

@@ -46,6 +46,36 @@ __global__ void __launch_bounds__(256) distance_pass(const uint8_t* __restrict__
   }
 }
 
+// One-sided variant for the octant fields: forward distance along +axis (DIR = +1) or -axis (DIR = -1) only.
+//   D(c) = min over k >= 0 of max(k, src(c + k * DIR))   with the border cell (at -1 or n) as an obstacle,
+// so after the three passes the value is the forward Chebyshev distance to the nearest occupied-or-border cell in
+// the octant (sx, sy, sz), i.e. the edge of the largest empty box that starts at the cell and extends forward.
+template <int AXIS, int DIR>
+__global__ void __launch_bounds__(256) forward_pass(const uint8_t* __restrict__ grid, const uint8_t* __restrict__ src,
+                                                     uint8_t* __restrict__ dst, int n, int log2n, int cap) {
+  const size_t total = (size_t)n << (2 * log2n);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i & (size_t)(n - 1)), y = (int)((i >> log2n) & (size_t)(n - 1)), z = (int)(i >> (2 * log2n));
+    const int c = AXIS == 0 ? x : (AXIS == 1 ? y : z);
+    const long long stride = (AXIS == 0 ? 1LL : (AXIS == 1 ? (long long)n : (long long)n * n)) * DIR;
+    int best = AXIS == 0 ? (__ldg(grid + i) ? 0 : cap) : (int)__ldg(src + i);
+    best = imin(best, DIR > 0 ? n - c : c + 1);      // the border cell ahead is an obstacle
+    for (int k = 1; k < best; k++) {                  // k < best <= distance to the border: the neighbour is inside the grid
+      const size_t j = (size_t)((long long)i + (long long)k * stride);
+      const int v = AXIS == 0 ? (__ldg(grid + j) ? 0 : cap) : (int)__ldg(src + j);
+      best = imin(best, imax(k, v));
+    }
+    dst[i] = (uint8_t)best;
+  }
+}
+
+template <int AXIS>
+static void launch_forward(int dir, unsigned blocks, const uint8_t* grid, const uint8_t* src, uint8_t* dst, int n, int log2n, int cap,
+                           cudaStream_t s) {
+  if (dir > 0) forward_pass<AXIS, 1><<<blocks, 256, 0, s>>>(grid, src, dst, n, log2n, cap);
+  else forward_pass<AXIS, -1><<<blocks, 256, 0, s>>>(grid, src, dst, n, log2n, cap);
+}
+
 __global__ void __launch_bounds__(256) pack_cells(const uint8_t* __restrict__ grid, const uint8_t* __restrict__ radius,
                                                    uint16_t* __restrict__ cells, int n, int log2n, unsigned long long* stats) {
   const int P = n + 2;
@@ -87,6 +117,34 @@ cudaError_t launch_repack(const uint8_t* d_grid, int n, int radius_cap, uint8_t*
   unsigned pblocks = (unsigned)(pwant > 148u * 64u ? 148u * 64u : pwant);
   pack_cells<<<pblocks, 256, 0, stream>>>(d_grid, tmp_a, d_cells, n, log2n, d_stats);
   if (launches) *launches = 4;
+  return cudaGetLastError();
+}
+
+// Eight octant arrays, d_cells + o * (n+2)^3 for o = (sx < 0) | (sy < 0) << 1 | (sz < 0) << 2.  The x pass is shared by
+// the four octants with the same sx, the y pass by the two with the same (sx, sy): 2 + 4 + 8 passes + 8 packs.
+// tmp_a: n^3 bytes (x pass), tmp_b: n^3 (y pass), tmp_c: n^3 (z pass).
+cudaError_t launch_repack_octants(const uint8_t* d_grid, int n, int radius_cap, uint8_t* tmp_a, uint8_t* tmp_b, uint8_t* tmp_c,
+                                  uint16_t* d_cells, unsigned long long* d_stats, cudaStream_t stream, int* launches) {
+  int log2n = 0;
+  while ((1 << log2n) < n) log2n++;
+  const size_t total = (size_t)n * n * n, ptotal = (size_t)(n + 2) * (n + 2) * (n + 2);
+  size_t want = (total + 255) / 256, pwant = (ptotal + 255) / 256;
+  const unsigned blocks = (unsigned)(want > 148u * 64u ? 148u * 64u : (want ? want : 1));
+  const unsigned pblocks = (unsigned)(pwant > 148u * 64u ? 148u * 64u : pwant);
+  const int cap = radius_cap < 1 ? 1 : (radius_cap > 255 ? 255 : radius_cap);
+  int count = 0;
+  for (int ox = 0; ox < 2; ox++) {
+    launch_forward<0>(ox ? -1 : 1, blocks, d_grid, nullptr, tmp_a, n, log2n, cap, stream); count++;
+    for (int oy = 0; oy < 2; oy++) {
+      launch_forward<1>(oy ? -1 : 1, blocks, d_grid, tmp_a, tmp_b, n, log2n, cap, stream); count++;
+      for (int oz = 0; oz < 2; oz++) {
+        launch_forward<2>(oz ? -1 : 1, blocks, d_grid, tmp_b, tmp_c, n, log2n, cap, stream); count++;
+        const int o = ox | (oy << 1) | (oz << 2);
+        pack_cells<<<pblocks, 256, 0, stream>>>(d_grid, tmp_c, d_cells + (size_t)o * ptotal, n, log2n, o == 0 ? d_stats : nullptr); count++;
+      }
+    }
+  }
+  if (launches) *launches = count;
   return cudaGetLastError();
 }
 

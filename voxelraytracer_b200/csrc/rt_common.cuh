@@ -148,6 +148,7 @@ struct DirConst {
   float jbias;           // (1 + 1/64) * invmax: a jump advances by r * invmax - jbias
   int dix, diy, diz;     // padded-index increment per axis step
   uint32_t ibias;        // constant folded into the jump's index computation (device path)
+  int oct;               // direction octant: (d.x < 0) | (d.y < 0) << 1 | (d.z < 0) << 2 -> which cell array to walk
 };
 
 VRT_HD float finf() { return u2f(0x7F800000u); }
@@ -168,13 +169,16 @@ VRT_HD void set_dir_const(DirConst& w, const V3& d, int P) {
   w.diz = d.z > 0.0f ? P * P : -(P * P);
   // float->int by magic number: bits(q + 1.5*2^23, rounded down) = 0x4B400000 + floor(q); fold "+1" per axis too
   w.ibias = (uint32_t)(0x4B400000u - 1u) * (uint32_t)(P * P + P + 1);
+  w.oct = (d.x < 0.0f ? 1 : 0) | (d.y < 0.0f ? 2 : 0) | (d.z < 0.0f ? 4 : 0);
 }
 
 // Everything a pixel needs, passed by value as a __grid_constant__ kernel parameter.
 struct FrameArgs {
   vrt_params p;
   const uint8_t* grid;      // raw R8 voxels, x + y*n + z*n*n (what glTexImage3D received, main.cpp:318)
-  const uint16_t* cells;    // repacked: (emptyRadius << 8) | voxelByte, (n+2)^3 with a one-cell border (rt_trace_fast.cuh)
+  const uint16_t* cells;    // repacked: (emptyRadius << 8) | voxelByte, (n+2)^3 with a one-cell border (rt_trace_fast.cuh);
+                            // with oct_stride != 0 there are 8 such arrays, one per direction octant (forward-box radii)
+  size_t oct_stride;        // cells between consecutive octant arrays, 0 = one isotropic array
   const uint8_t* atlas;     // RGBA8, atlasSize^2, GL memory order
   uint8_t* out_rgba8;       // tile, compact rows
   float* out_f32;           // optional unquantised frame

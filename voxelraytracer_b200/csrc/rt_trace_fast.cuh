@@ -201,9 +201,9 @@ struct FastTracer {
   static VRT_HD bool shadow(Ctx& cx, const Ray& r, const Hit&) {
     cx.count(CNT_SHADOW);
     const int n = cx.f.p.size, P = n + 2;
-    const uint16_t* cells = cx.f.cells;
-    const float tcap = cx.f.p.maxRayLength - r.len;
     const DirConst& k = cx.f.sun;                          // shadow rays all point at the sun (voxel.glsl:191-201)
+    const uint16_t* cells = cx.f.cells + (size_t)k.oct * cx.f.oct_stride;
+    const float tcap = cx.f.p.maxRayLength - r.len;
     Walk w;
     if (!begin(w, k, r, cx.f.fsize, n, P)) return false;
     uint32_t rad = load_cell(cells, w.idx) >> 8;
@@ -219,9 +219,9 @@ struct FastTracer {
     Hit h;
     h.found = false;
     const int n = cx.f.p.size, P = n + 2;
-    const uint16_t* cells = cx.f.cells;
     DirConst k;
     set_dir_const(k, r.dir, P);
+    const uint16_t* cells = cx.f.cells + (size_t)k.oct * cx.f.oct_stride;
     Walk w;
     if (!begin(w, k, r, cx.f.fsize, n, P)) return h;
     float tcap = cx.f.p.maxRayLength - r.len;
@@ -269,6 +269,7 @@ struct FastTracer {
       // Restart the walk on the face just crossed.  The cell on the parent side is the medium cell the ray
       // was in; begin() derives it from face_nsign (the normal points back into that cell).
       set_dir_const(k, r.dir, P);
+      cells = cx.f.cells + (size_t)k.oct * cx.f.oct_stride;
       if (!begin(w, k, r, cx.f.fsize, n, P)) return h;
       tcap = cx.f.p.maxRayLength - r.len;
       rad = 0u;                                            // first move from the restart cell: one plain step

@@ -21,7 +21,9 @@ struct vrt_ctx {
   // chunk
   int size = 0, log2n = 0;
   uint8_t* d_grid = nullptr;       // n^3 raw bytes
-  uint16_t* d_cells = nullptr;     // (n+2)^3 traversal cells
+  uint16_t* d_cells = nullptr;     // (n+2)^3 traversal cells, x 8 with octant fields
+  int opt_octants = 1;             // VRT_OPT_OCTANT_FIELDS (applies to the next upload)
+  int octants = 0;                 // what d_cells holds
   // atlas
   uint8_t* d_atlas = nullptr;
   int atlasSize = 0, atlasTextureSize = 0;
@@ -122,29 +124,30 @@ int vrt_destroy(vrt_ctx* ctx) {
 
 static int repack_locked(vrt_ctx* ctx, int size, cudaStream_t s) {
   const size_t n3 = (size_t)size * size * size, p3 = (size_t)(size + 2) * (size + 2) * (size + 2);
+  const int oct = ctx->opt_octants ? 1 : 0;
   if (ctx->d_cells) { cudaFree(ctx->d_cells); ctx->d_cells = nullptr; }
-  CU(cudaMalloc((void**)&ctx->d_cells, p3 * sizeof(uint16_t)));
-  uint8_t *ta = nullptr, *tb = nullptr;
-  CU(cudaMalloc((void**)&ta, n3));
-  cudaError_t e = cudaMalloc((void**)&tb, n3);
-  if (e != cudaSuccess) { cudaFree(ta); return fail(ctx, VRT_E_OOM, "repack scratch: %s", cudaGetErrorString(e)); }
+  CU(cudaMalloc((void**)&ctx->d_cells, p3 * sizeof(uint16_t) * (oct ? 8 : 1)));
+  uint8_t* tmp = nullptr;                                  // 2 (isotropic) or 3 (octants) scratch volumes of n^3 bytes
+  CU(cudaMalloc((void**)&tmp, n3 * (oct ? 3 : 2)));
   cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * 8, s);
   int launches = 0;
   // Radius cap: 255 fits the byte; for big chunks a smaller cap bounds the build time (O(radius) per voxel).
   const int cap = size <= 256 ? 255 : 96;
-  e = launch_repack(ctx->d_grid, size, cap, ta, tb, ctx->d_cells, ctx->d_stats, s, &launches);
+  cudaError_t e = oct ? launch_repack_octants(ctx->d_grid, size, cap, tmp, tmp + n3, tmp + 2 * n3, ctx->d_cells, ctx->d_stats, s, &launches)
+                      : launch_repack(ctx->d_grid, size, cap, tmp, tmp + n3, ctx->d_cells, ctx->d_stats, s, &launches);
   ctx->launches += launches;
   cudaError_t e2 = cudaStreamSynchronize(s);
-  cudaFree(ta); cudaFree(tb);
+  cudaFree(tmp);
   if (e != cudaSuccess || e2 != cudaSuccess)
     return fail(ctx, VRT_E_CUDA, "repack: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
   unsigned long long occ = 0;
   CU(cudaMemcpy(&occ, ctx->d_stats, sizeof(occ), cudaMemcpyDeviceToHost));
   ctx->size = size;
+  ctx->octants = oct;
   ctx->log2n = 0;
   while ((1 << ctx->log2n) < size) ctx->log2n++;
-  ctx->info.size = size; ctx->info.pitch = size + 2; ctx->info.radius_cap = cap; ctx->info.reserved = 0;
-  ctx->info.cells_total = (int64_t)p3; ctx->info.voxels_occupied = (int64_t)occ;
+  ctx->info.size = size; ctx->info.pitch = size + 2; ctx->info.radius_cap = cap; ctx->info.octants = oct ? 8 : 1;
+  ctx->info.cells_total = (int64_t)p3 * (oct ? 8 : 1); ctx->info.voxels_occupied = (int64_t)occ;
   return VRT_OK;
 }
 
@@ -222,6 +225,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   memset(&a, 0, sizeof(a));
   a.p = *p;
   a.grid = ctx->d_grid; a.cells = ctx->d_cells; a.atlas = ctx->d_atlas;
+  a.oct_stride = ctx->octants ? (size_t)(ctx->size + 2) * (ctx->size + 2) * (ctx->size + 2) : 0;
   if (!d_out && (p->flags & VRT_FLAG_OUT_FRAME)) return fail(ctx, VRT_E_INVALID, "render: VRT_FLAG_OUT_FRAME needs vrt_render_to");
   if (!d_out) {
     if ((rc = ensure(ctx, &ctx->d_fb, &ctx->fb_bytes, (size_t)npix * 4))) return rc;
@@ -353,12 +357,20 @@ int vrt_grid_info_get(vrt_ctx* ctx, vrt_grid_info* out) {
 int vrt_read_cells(vrt_ctx* ctx, uint16_t* host, size_t count) {
   if (!ctx || !host) return fail(ctx, VRT_E_INVALID, "vrt_read_cells: NULL argument");
   if (!ctx->d_cells) return fail(ctx, VRT_E_NOT_READY, "vrt_read_cells: no grid uploaded");
-  const size_t p3 = (size_t)(ctx->size + 2) * (ctx->size + 2) * (ctx->size + 2);
-  if (count != p3) return fail(ctx, VRT_E_INVALID, "vrt_read_cells: count %zu != (size+2)^3 = %zu", count, p3);
+  const size_t p3 = (size_t)(ctx->size + 2) * (ctx->size + 2) * (ctx->size + 2) * (ctx->octants ? 8 : 1);
+  if (count != p3) return fail(ctx, VRT_E_INVALID, "vrt_read_cells: count %zu != cells_total = %zu", count, p3);
   int rc = bind(ctx);
   if (rc) return rc;
   CU(cudaMemcpy(host, ctx->d_cells, p3 * sizeof(uint16_t), cudaMemcpyDeviceToHost));
   return VRT_OK;
+}
+
+int vrt_set_option(vrt_ctx* ctx, int option, int value) {
+  if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_set_option: NULL ctx");
+  switch (option) {
+    case VRT_OPT_OCTANT_FIELDS: ctx->opt_octants = value ? 1 : 0; return VRT_OK;
+    default: return fail(ctx, VRT_E_INVALID, "vrt_set_option: unknown option %d", option);
+  }
 }
 
 int vrt_temporal_blend(vrt_ctx* ctx, const void* d_new, void* d_acc, int64_t npix, float alpha, void* stream) {

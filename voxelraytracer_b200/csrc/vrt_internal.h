@@ -18,6 +18,10 @@ cudaError_t launch_render_persistent(const FrameArgs& args, bool flat, unsigned 
 cudaError_t launch_repack(const uint8_t* d_grid, int n, int radius_cap, uint8_t* tmp_a, uint8_t* tmp_b, uint16_t* d_cells,
                           unsigned long long* d_stats, cudaStream_t stream, int* launches);
 
+// Octant fields: 8 arrays of (n+2)^3 cells at d_cells (see repack.cu).  tmp_a/b/c: n^3 bytes each.
+cudaError_t launch_repack_octants(const uint8_t* d_grid, int n, int radius_cap, uint8_t* tmp_a, uint8_t* tmp_b, uint8_t* tmp_c,
+                                  uint16_t* d_cells, unsigned long long* d_stats, cudaStream_t stream, int* launches);
+
 // temporal.cu
 cudaError_t launch_temporal_blend(const uint8_t* d_new, uint8_t* d_acc, int64_t npix, float alpha, cudaStream_t stream);
 
