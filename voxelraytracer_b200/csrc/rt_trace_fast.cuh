@@ -83,13 +83,19 @@ struct FastTracer {
     if (sz) w.tmax.z += k.tdel.z;
   }
 
-  // Jump inside the empty cube promised by radius r (r >= 2): advance by (r - 1 - 1/64) cells of dominant-axis
-  // travel, then re-derive the cell and the plane times from the position.  False if the length cap forbids it.
-  static VRT_HD bool jump(Walk& w, const DirConst& k, uint32_t r, float tcap, int P) {
+  // Jump inside the empty box promised by radius r (r >= 2): advance by (r - 1 - 1/64) cells of dominant-axis
+  // travel, then re-derive the cell and the plane times from the position.  `tlim` is the largest float below the
+  // length cap: a jump that would pass the cap is shortened to land just before it (still inside the empty box), so
+  // that the steps the reference would still take from there - including the last one, which may overshoot the cap and
+  // hit (voxel.glsl:317-353) - are taken and tested one by one.  False only if that leaves no progress.
+  // After such a shortened jump `tlim` is set below every walk time, so the rest of the walk is plain steps (a second
+  // shortened jump could land on the same point again and, with plane times rounded behind it, never terminate).
+  static VRT_HD bool jump(Walk& w, const DirConst& k, uint32_t r, float& tlim, int P) {
     // (float)r without a conversion instruction: 2^23 + r has r in its low mantissa bits
     const float rf = u2f(0x4B000000u | r) - 8388608.0f;
-    const float tn = fmaf(rf, k.invmax, w.t - k.jbias);
-    if (!(tn < tcap)) return false;
+    float tn = fmaf(rf, k.invmax, w.t - k.jbias);
+    if (!(tn < tlim)) { tn = tlim; tlim = -1.0f; }
+    if (!(tn > w.t)) return false;
     const float qx = fmaf(tn, k.d.x, w.o.x), qy = fmaf(tn, k.d.y, w.o.y), qz = fmaf(tn, k.d.z, w.o.z);
 #if defined(__CUDA_ARCH__)
     // floor + float->int on the FMA/ALU pipes: add 1.5*2^23 rounding DOWN; the sum's low bits are floor(q)
@@ -105,16 +111,6 @@ struct FastTracer {
     w.tmax.z = ((fz + k.off.z) - w.o.z) * k.inv.z;
     w.t = tn;
     return true;
-  }
-
-  // Moves from an empty (or untested start) cell with radius r to the next cell that must be looked at.
-  // Precondition: w.t < tcap.  The reference takes a step only while rayLength < u_MaxRayLength (voxel.glsl:273,317),
-  // so the second step of an r = 2 advance is taken only if the first one ended below the cap; the caller's
-  // loop-top test then ends the walk.
-  static VRT_HD void advance(Walk& w, const DirConst& k, uint32_t r, float tcap, int P) {
-    if (r >= (uint32_t)VRT_JUMP_MIN && jump(w, k, r, tcap, P)) return;
-    step(w, k);
-    if (r >= 2u && w.t < tcap) step(w, k);
   }
 
   // Start of a ray.  Returns false when the ray can never touch the chunk.
@@ -184,12 +180,19 @@ struct FastTracer {
   // (occupied or border) and returns that cell's value; returns 0xFFFFFFFF when the length cap ends the walk first.
   // This is the hot loop of the whole path: one 2-byte load per iteration, nothing else touches memory.
   static VRT_HD uint32_t walk_air(Ctx& cx, Walk& w, const DirConst& k, const uint16_t* cells, uint32_t rad, float tcap, int P) {
+    if (!(tcap > 0.0f)) return 0xFFFFFFFFu;                // already at the length cap (w.t >= 0 always)
+    float tlim = u2f(f2u(tcap) - 1u);                      // next float below tcap
     for (;;) {
       // a successful jump implies w.t < tn < tcap, so only the stepping path tests the cap itself
-      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tcap, P))) {
+      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tlim, P))) {
         if (!(w.t < tcap)) return 0xFFFFFFFFu;
-        step(w, k);
-        if (rad >= 2u && w.t < tcap) step(w, k);
+        // one step, or two for rad == 2, as a real (not if-converted) loop: predicated-off instructions of an unneeded
+        // second step would still cost issue slots, and issue is the bound
+        uint32_t left = rad;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+        do { step(w, k); } while (--left == 1u && w.t < tcap);
       }
       cx.count(CNT_ACTUAL_STEPS);
       const uint32_t c = load_cell(cells, w.idx);
