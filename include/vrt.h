@@ -175,6 +175,10 @@ int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes
 /* ---- temporal accumulation pass (res/shaders/temporal.glsl:13-19; main.cpp:363-376,388-393) ----
  * acc = alpha * new + (1 - alpha) * acc on RGBA8 device buffers, n pixels. */
 int vrt_temporal_blend(vrt_ctx* ctx, const void* d_new_rgba8, void* d_acc_rgba8, int64_t npix, float alpha, void* stream);
+/* Same pass in the reference's three-target form: out = alpha * new + (1 - alpha) * old, with `new` = rayTraceFrameBuffer,
+ * `old` = lastFrameBuffer, `out` = currentFrameBuffer (main.cpp:363-376); out may alias old. */
+int vrt_temporal_filter(vrt_ctx* ctx, const void* d_new_rgba8, const void* d_old_rgba8, void* d_out_rgba8, int64_t npix, float alpha,
+                        void* stream);
 
 /* ---- cross-process framebuffer sharing for the fused render+gather path (CUDA IPC) ---- */
 #define VRT_IPC_HANDLE_BYTES 64

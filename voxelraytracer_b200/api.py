@@ -24,7 +24,7 @@ EXPORTS = [
     "vrt_upload_grid_device", "vrt_upload_atlas", "vrt_render", "vrt_render_to", "vrt_render_host", "vrt_tile_pixels",
     "vrt_framebuffer_device", "vrt_read_framebuffer", "vrt_read_debug_maps", "vrt_read_float_frame", "vrt_reset_counters",
     "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells", "vrt_set_option",
-    "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_device", "vrt_temporal_blend",
+    "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_device", "vrt_temporal_blend", "vrt_temporal_filter",
     "vrt_ipc_alloc_frame", "vrt_ipc_open", "vrt_ipc_close", "vrt_scene_fill", "vrt_noise_heightmap", "vrt_atlas_synthetic",
     "vrt_atlas_pack", "vrt_camera_invpv", "vrt_sun_dir",
 ]
@@ -121,6 +121,7 @@ def load_library():
         "vrt_copy_to_host": (i32, [vp, vp, vp, C.c_size_t, vp]),
         "vrt_copy_to_device": (i32, [vp, vp, vp, C.c_size_t, vp]),
         "vrt_temporal_blend": (i32, [vp, vp, vp, i64, f32, vp]),
+        "vrt_temporal_filter": (i32, [vp, vp, vp, vp, i64, f32, vp]),
         "vrt_ipc_alloc_frame": (i32, [vp, C.c_size_t, C.POINTER(vp), vp]),
         "vrt_ipc_open": (i32, [vp, vp, C.POINTER(vp)]),
         "vrt_ipc_close": (i32, [vp, vp]),
@@ -329,6 +330,9 @@ class Context:
 
     def temporal_blend(self, d_new, d_acc, npix, alpha, stream=None):
         self._check(self.lib.vrt_temporal_blend(self.h, d_new, d_acc, npix, alpha, stream))
+
+    def temporal_filter(self, d_new, d_old, d_out, npix, alpha, stream=None):
+        self._check(self.lib.vrt_temporal_filter(self.h, d_new, d_old, d_out, npix, alpha, stream))
 
     # memory helpers
     def host_alloc(self, nbytes):

@@ -16,27 +16,30 @@ __device__ __forceinline__ unsigned blend_px(unsigned nw, unsigned ol, float alp
   return out;
 }
 
-__global__ void __launch_bounds__(256) temporal_blend_kernel(const uint8_t* __restrict__ nw, uint8_t* __restrict__ acc, int64_t npix, float alpha) {
+// out may alias old (the in-place form); each thread reads its own element before writing it.
+__global__ void __launch_bounds__(256) temporal_blend_kernel(const uint8_t* __restrict__ nw, const uint8_t* old, uint8_t* out, int64_t npix, float alpha) {
   const int64_t nvec = npix / 4;
   const uint4* n4 = reinterpret_cast<const uint4*>(nw);
-  uint4* a4 = reinterpret_cast<uint4*>(acc);
+  const uint4* o4 = reinterpret_cast<const uint4*>(old);
+  uint4* a4 = reinterpret_cast<uint4*>(out);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-    uint4 a = __ldg(n4 + i), b = a4[i];
+    uint4 a = __ldg(n4 + i), b = o4[i];
     b.x = blend_px(a.x, b.x, alpha); b.y = blend_px(a.y, b.y, alpha); b.z = blend_px(a.z, b.z, alpha); b.w = blend_px(a.w, b.w, alpha);
     a4[i] = b;
   }
   // tail (npix not a multiple of 4)
   const unsigned* n1 = reinterpret_cast<const unsigned*>(nw);
-  unsigned* a1 = reinterpret_cast<unsigned*>(acc);
+  const unsigned* o1 = reinterpret_cast<const unsigned*>(old);
+  unsigned* a1 = reinterpret_cast<unsigned*>(out);
   for (int64_t i = nvec * 4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (int64_t)gridDim.x * blockDim.x)
-    a1[i] = blend_px(n1[i], a1[i], alpha);
+    a1[i] = blend_px(n1[i], o1[i], alpha);
 }
 
-cudaError_t launch_temporal_blend(const uint8_t* d_new, uint8_t* d_acc, int64_t npix, float alpha, cudaStream_t stream) {
+cudaError_t launch_temporal_blend(const uint8_t* d_new, const uint8_t* d_old, uint8_t* d_out, int64_t npix, float alpha, cudaStream_t stream) {
   if (npix <= 0) return cudaSuccess;
   int64_t want = (npix / 4 + 255) / 256;
   unsigned blocks = (unsigned)(want > 148 * 16 ? 148 * 16 : (want < 1 ? 1 : want));
-  temporal_blend_kernel<<<blocks, 256, 0, stream>>>(d_new, d_acc, npix, alpha);
+  temporal_blend_kernel<<<blocks, 256, 0, stream>>>(d_new, d_old, d_out, npix, alpha);
   return cudaGetLastError();
 }
 

@@ -378,7 +378,17 @@ int vrt_temporal_blend(vrt_ctx* ctx, const void* d_new, void* d_acc, int64_t npi
   if (((uintptr_t)d_new | (uintptr_t)d_acc) & 15) return fail(ctx, VRT_E_INVALID, "vrt_temporal_blend: buffers must be 16-byte aligned");
   int rc = bind(ctx);
   if (rc) return rc;
-  CU(launch_temporal_blend((const uint8_t*)d_new, (uint8_t*)d_acc, npix, alpha, (cudaStream_t)stream));
+  CU(launch_temporal_blend((const uint8_t*)d_new, (const uint8_t*)d_acc, (uint8_t*)d_acc, npix, alpha, (cudaStream_t)stream));
+  ctx->launches += 1;
+  return VRT_OK;
+}
+
+int vrt_temporal_filter(vrt_ctx* ctx, const void* d_new, const void* d_old, void* d_out, int64_t npix, float alpha, void* stream) {
+  if (!ctx || !d_new || !d_old || !d_out || npix < 0) return fail(ctx, VRT_E_INVALID, "vrt_temporal_filter: bad argument");
+  if (((uintptr_t)d_new | (uintptr_t)d_old | (uintptr_t)d_out) & 15) return fail(ctx, VRT_E_INVALID, "vrt_temporal_filter: buffers must be 16-byte aligned");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(launch_temporal_blend((const uint8_t*)d_new, (const uint8_t*)d_old, (uint8_t*)d_out, npix, alpha, (cudaStream_t)stream));
   ctx->launches += 1;
   return VRT_OK;
 }
