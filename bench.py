@@ -62,7 +62,7 @@ WORKLOAD_DESC = {
 }
 I_STEP = 16          # algorithmic thread-instructions per reference DDA step
 # dram__bytes_read.sum + dram__bytes_write.sum per render_kernel launch from the committed `ncu --set full` capture (profiles/)
-NCU_TRAFFIC = {"c2": 2.8e6}
+NCU_TRAFFIC = {"c2": 3.3e6, "c5": 3.4e9}   # profiles/r01_ncu_c2_final.txt, r01_ncu_c5.txt
 
 
 def parse():
@@ -492,7 +492,8 @@ def run_ours(args):
             "actual_steps_per_frame": act_all / frames_total,
             "gsteps_per_s": steps_all / t_step_total / 1e9,
             "roofline": {"bound": "issue", "achieved": ach_issue / 1e12, "peak": p_issue / 1e12, "unit": "Tinstr/s", "frac": ach_issue / p_issue,
-                         "traffic": None, "peak_source": "%d SM x 4 schedulers x 32 lanes x sampled SM clock %.0f MHz" % (sms, f_mhz),
+                         "traffic": NCU_TRAFFIC.get(args.workload), "traffic_unit": "DRAM bytes per launch (ncu --set full)",
+                         "peak_source": "%d SM x 4 schedulers x 32 lanes x sampled SM clock %.0f MHz" % (sms, f_mhz),
                          "algorithmic": "%d thread-instr per reference DDA step x reference steps (SURVEY.md 8(d))" % I_STEP},
             "roofline_hbm": {"bound": "hbm", "achieved": bytes_per_launch / per_launch_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                              "frac": bytes_per_launch / per_launch_s / 1e9 / hbm_peak, "traffic": NCU_TRAFFIC.get(args.workload),
