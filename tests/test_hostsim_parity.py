@@ -98,3 +98,23 @@ def test_cells_radius_is_exact_chebyshev_distance():
             assert (w >> 8) >= (v >> 8)        # a forward box is never smaller than the centred cube
     for cells in (iso, octs[0], octs[7]):
         assert (cells[0] == 0).all() and (cells[:, 0] == 0).all() and (cells[:, :, -1] == 0).all()
+
+
+def test_fast_tracer_with_noise_uniforms():
+    """Non-zero noise uniforms.  Primary-ray noise: the fast traversal generates the jittered ray with the pinned
+    arithmetic, so the usual caps hold.  Reflection / refraction noise hashes the HIT POINT, whose last ulps differ between
+    the fast walk and the replayed recurrence: bounce rays get a different (equally random) offset, so only the primary
+    hit map is comparable; bit-exact noise needs VRT_FLAG_EXACT (test_noise_uniforms_exact_mode)."""
+    for sc, pose, fl in (("glass_cube32", "start", vrt.FLAG_COLOR_ONLY), ("terrain32", "terrain32_above", 0)):
+        grid, n, atlas, ts = scene(sc)
+        p = make_params(320, 180, sc, pose, fl, noise=(0.01, 0.0, 0.0), time=9.0)
+        o = oracle_render(p, grid, atlas)
+        f = hostsim_render(p, grid, atlas, 1)
+        bad = int(((f.hit != o.hit) | (f.bounces != o.bounces)).sum())
+        assert bad <= max(3, int(1e-4 * 320 * 180)), (sc, bad)
+        assert (rms255(f.rgba8, o.rgba8) <= 1.0).all(), rms255(f.rgba8, o.rgba8)
+        p = make_params(320, 180, sc, pose, fl, noise=(0.01, 0.08, 0.05), time=9.0)
+        o = oracle_render(p, grid, atlas)
+        f = hostsim_render(p, grid, atlas, 1)
+        assert int((f.hit != o.hit).sum()) <= max(3, int(1e-4 * 320 * 180)), sc       # primary hit map
+        assert np.abs(f.rgba8.astype(float).mean(axis=0) - o.rgba8.astype(float).mean(axis=0)).max() < 2.0   # same image statistically

@@ -205,7 +205,10 @@ VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
     fr[i] = (xy + m[8 + i] * 1.0f) + m[12 + i] * 1.0f;
   }
   V3 vnear, vdir;
-  if (Tracer::Ctx::kLean) {   // reciprocal-multiply instead of three IEEE divisions each
+  // The hash behind u_RayNoise amplifies a last-ulp difference of its inputs (vnear, direction) into a different
+  // random offset, so with primary-ray noise the fast traversal generates the ray with the pinned arithmetic too.
+  const bool lean_gen = Tracer::Ctx::kLean && p.rayNoise == 0.0f;
+  if (lean_gen) {   // reciprocal-multiply instead of three IEEE divisions each
     const float iw = 1.0f / nr[3], jw = 1.0f / fr[3];
     vnear = mk3(nr[0] * iw, nr[1] * iw, nr[2] * iw);
     vdir = mk3(fr[0] * jw - vnear.x, fr[1] * jw - vnear.y, fr[2] * jw - vnear.z);
@@ -213,14 +216,13 @@ VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
     vnear = mk3(nr[0] / nr[3], nr[1] / nr[3], nr[2] / nr[3]);
     vdir = mk3(fr[0] / fr[3] - vnear.x, fr[1] / fr[3] - vnear.y, fr[2] / fr[3] - vnear.z);
   }
-
   constexpr int kStack = 8;  // maxReflections + maxTransparencies + 1 <= 8 (checked by the API)
   Ray stack[kStack];         // only bounce rays ever live here; the primary ray stays in registers
   float half = cx.f.fsize * 0.5f;
   Ray r;
   r.pos = mk3(vnear.x + half, vnear.y + half, vnear.z + half);
   // the shader normalises twice (voxel.glsl:430 and :139); with zero noise the lean path does it once
-  r.dir = (Tracer::Ctx::kLean && p.rayNoise == 0.0f) ? normalize3_lean(vdir) : cx.jitter(normalize3(vdir), vnear, p.rayNoise);
+  r.dir = lean_gen ? normalize3_lean(vdir) : randomize_direction(normalize3(vdir), vnear, p.rayNoise, p.time);
   r.len = 0.0f; r.energy = 1.0f; r.medium = 0; r.nrefl = 0; r.ntrans = 0; r.face_axis = -1; r.face_nsign = 0.0f;
   int n = 0, popped = 0;
   V3 color = mk3(0.0f, 0.0f, 0.0f);
