@@ -171,6 +171,10 @@ int vrt_device_free(vrt_ctx* ctx, void* p);
 int vrt_synchronize(vrt_ctx* ctx, void* stream);
 int vrt_copy_to_host(vrt_ctx* ctx, void* host, const void* d_src, size_t bytes, void* stream);   /* async on `stream`, then synchronised */
 int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes, void* stream); /* async on `stream`, then synchronised */
+/* Not synchronised: `host` should be pinned (vrt_host_alloc) and must not be read before vrt_synchronize(ctx, stream).
+ * With vrt_render_to on the same stream this is the double-buffered form of vrt_render_host: frame i's copy to the host
+ * overlaps frame i+1's render on another stream. */
+int vrt_copy_to_host_async(vrt_ctx* ctx, void* host, const void* d_src, size_t bytes, void* stream);
 
 /* ---- temporal accumulation pass (res/shaders/temporal.glsl:13-19; main.cpp:363-376,388-393) ----
  * acc = alpha * new + (1 - alpha) * acc on RGBA8 device buffers, n pixels. */

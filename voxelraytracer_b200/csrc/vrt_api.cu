@@ -440,6 +440,14 @@ int vrt_copy_to_host(vrt_ctx* ctx, void* host, const void* d_src, size_t bytes, 
   return VRT_OK;
 }
 
+int vrt_copy_to_host_async(vrt_ctx* ctx, void* host, const void* d_src, size_t bytes, void* stream) {
+  if (!ctx || !host || !d_src) return fail(ctx, VRT_E_INVALID, "vrt_copy_to_host_async: NULL argument");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(host, d_src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return VRT_OK;
+}
+
 int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes, void* stream) {
   if (!ctx || !d_dst || !host) return fail(ctx, VRT_E_INVALID, "vrt_copy_to_device: NULL argument");
   int rc = bind(ctx);
