@@ -162,7 +162,8 @@ VRT_HD void set_dir_const(DirConst& w, const V3& d, int P) {
   w.inv = mk3(zx ? finf() : 1.0f / d.x, zy ? finf() : 1.0f / d.y, zz ? finf() : 1.0f / d.z);
   w.tdel = mk3(zx ? 0.0f : fabsf(w.inv.x), zy ? 0.0f : fabsf(w.inv.y), zz ? 0.0f : fabsf(w.inv.z));
   w.off = mk3(d.x >= 0.0f ? 1.0f : 0.0f, d.y >= 0.0f ? 1.0f : 0.0f, d.z >= 0.0f ? 1.0f : 0.0f);
-  w.invmax = 1.0f / fmaxf(fabsf(d.x), fmaxf(fabsf(d.y), fabsf(d.z)));
+  // 1 / max|d| == min |1/d| exactly (correctly rounded reciprocals are monotone); zero components are +inf and drop out
+  w.invmax = fminf(fabsf(w.inv.x), fminf(fabsf(w.inv.y), fabsf(w.inv.z)));
   w.jbias = 1.015625f * w.invmax;
   w.dix = d.x > 0.0f ? 1 : -1;
   w.diy = d.y > 0.0f ? P : -P;
@@ -189,6 +190,10 @@ struct FrameArgs {
   DirConst sun;             // walk constants of sun_unit for this chunk (every shadow ray shares them)
   float fsize;              // (float)u_Size
   float day;                // max(u_SunDir.y, 0)
+  float tex_scale;          // u_AtlasTextureSize / u_AtlasSize (fast traversal's texture coordinates)
+  int pitch;                // n + 2
+  uint32_t ibias;           // jump index constant (see set_dir_const), per frame so that it is read from the constant bank
+  const uint16_t* sun_cells;  // cells + sun.oct * oct_stride: the array every shadow ray walks
   int rows_local;           // number of compact rows this launch writes
   int log2n;
 };
@@ -199,9 +204,13 @@ inline bool finish_frame_args(FrameArgs& a) {
   a.sun_unit = normalize3(mk3(a.p.sunDir[0], a.p.sunDir[1], a.p.sunDir[2]));
   a.fsize = (float)a.p.size;
   a.day = gmax(a.p.sunDir[1], 0.0f);
+  a.tex_scale = a.p.atlasSize > 0 ? (float)a.p.atlasTextureSize / (float)a.p.atlasSize : 0.0f;
   a.log2n = 0;
   while ((1 << a.log2n) < a.p.size) a.log2n++;
   set_dir_const(a.sun, a.sun_unit, a.p.size + 2);
+  a.pitch = a.p.size + 2;
+  a.ibias = a.sun.ibias;
+  a.sun_cells = a.cells ? a.cells + (size_t)a.sun.oct * a.oct_stride : nullptr;
   return (1 << a.log2n) == a.p.size;
 }
 

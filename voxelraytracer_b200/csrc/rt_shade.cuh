@@ -75,8 +75,13 @@ struct PixelCtx {
     MatProps m = material_of<false>(voxel);
     float fa = a - floorf(a), fb = b - floorf(b);
     float ts = (float)f.p.atlasTextureSize, as = (float)f.p.atlasSize;
-    *u = (fa + (float)m.tx) * ts / as;
-    *v = 1.0f - ((1.0f - fb) + (float)m.ty) * ts / as;
+    if (LEAN) {   // one per-frame ratio instead of two divisions; identical when both sizes are powers of two (16/32, 128/256)
+      *u = (fa + (float)m.tx) * f.tex_scale;
+      *v = 1.0f - ((1.0f - fb) + (float)m.ty) * f.tex_scale;
+    } else {
+      *u = (fa + (float)m.tx) * ts / as;
+      *v = 1.0f - ((1.0f - fb) + (float)m.ty) * ts / as;
+    }
   }
 
   VRT_HD V3 normal_of(const Hit& h) const {

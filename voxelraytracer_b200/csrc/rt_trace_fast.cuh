@@ -90,7 +90,7 @@ struct FastTracer {
   // hit (voxel.glsl:317-353) - are taken and tested one by one.  False only if that leaves no progress.
   // After such a shortened jump `tlim` is set below every walk time, so the rest of the walk is plain steps (a second
   // shortened jump could land on the same point again and, with plane times rounded behind it, never terminate).
-  static VRT_HD bool jump(Walk& w, const DirConst& k, uint32_t r, float& tlim, int P) {
+  static VRT_HD bool jump(Walk& w, const DirConst& k, uint32_t r, float& tlim, int P, uint32_t ibias) {
     // (float)r without a conversion instruction: 2^23 + r has r in its low mantissa bits
     const float rf = u2f(0x4B000000u | r) - 8388608.0f;
     float tn = fmaf(rf, k.invmax, w.t - k.jbias);
@@ -101,7 +101,7 @@ struct FastTracer {
     // floor + float->int on the FMA/ALU pipes: add 1.5*2^23 rounding DOWN; the sum's low bits are floor(q)
     const float mx = __fadd_rd(qx, 12582912.0f), my = __fadd_rd(qy, 12582912.0f), mz = __fadd_rd(qz, 12582912.0f);
     const float fx = mx - 12582912.0f, fy = my - 12582912.0f, fz = mz - 12582912.0f;
-    w.idx = (f2u(mz) * (uint32_t)P + f2u(my)) * (uint32_t)P + f2u(mx) - k.ibias;
+    w.idx = (f2u(mz) * (uint32_t)P + f2u(my)) * (uint32_t)P + f2u(mx) - ibias;
 #else
     const float fx = floorf(qx), fy = floorf(qy), fz = floorf(qz);
     w.idx = (uint32_t)(((int)fz + 1) * P + ((int)fy + 1)) * (uint32_t)P + (uint32_t)((int)fx + 1);
@@ -184,7 +184,7 @@ struct FastTracer {
     float tlim = u2f(f2u(tcap) - 1u);                      // next float below tcap
     for (;;) {
       // a successful jump implies w.t < tn < tcap, so only the stepping path tests the cap itself
-      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tlim, P))) {
+      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tlim, P, cx.f.ibias))) {
         if (!(w.t < tcap)) return 0xFFFFFFFFu;
         // one step, or two for rad == 2, as a real (not if-converted) loop: predicated-off instructions of an unneeded
         // second step would still cost issue slots, and issue is the bound
@@ -203,9 +203,9 @@ struct FastTracer {
 
   static VRT_HD bool shadow(Ctx& cx, const Ray& r, const Hit&) {
     cx.count(CNT_SHADOW);
-    const int n = cx.f.p.size, P = n + 2;
+    const int n = cx.f.p.size, P = cx.f.pitch;
     const DirConst& k = cx.f.sun;                          // shadow rays all point at the sun (voxel.glsl:191-201)
-    const uint16_t* cells = cx.f.cells + (size_t)k.oct * cx.f.oct_stride;
+    const uint16_t* cells = cx.f.sun_cells;
     const float tcap = cx.f.p.maxRayLength - r.len;
     Walk w;
     if (!begin(w, k, r, cx.f.fsize, n, P)) return false;
@@ -221,7 +221,7 @@ struct FastTracer {
   static VRT_HD Hit march(Ctx& cx, Ray& r) {
     Hit h;
     h.found = false;
-    const int n = cx.f.p.size, P = n + 2;
+    const int n = cx.f.p.size, P = cx.f.pitch;
     DirConst k;
     set_dir_const(k, r.dir, P);
     const uint16_t* cells = cx.f.cells + (size_t)k.oct * cx.f.oct_stride;
