@@ -80,6 +80,7 @@ def parse():
                     help="weak: one full frame per GPU per step (pose batch); strong: ONE frame per step, 16-row bands dealt round-robin")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--octants", type=int, default=1, choices=[0, 1], help="VRT_OPT_OCTANT_FIELDS (tuning comparison; 1 = default)")
+    ap.add_argument("--radius-cap", type=int, default=0, help="VRT_OPT_RADIUS_CAP (tuning comparison; 0 = default)")
     ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
     return ap.parse_args()
 
@@ -244,6 +245,7 @@ def run_ours(args):
     grid, n, atlas, ts = common.scene(sc)
     ctx = vrt.Context(local)
     ctx.set_option(vrt.OPT_OCTANT_FIELDS, args.octants)
+    ctx.set_option(vrt.OPT_RADIUS_CAP, args.radius_cap)
     t_up0 = time.perf_counter()
     ctx.upload_grid(grid, n)
     t_upload = time.perf_counter() - t_up0

@@ -160,7 +160,10 @@ int vrt_grid_info_get(vrt_ctx* ctx, vrt_grid_info* out);
 int vrt_read_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count); /* count must be cells_total */
 
 /* Tuning options; take effect at the next vrt_upload_grid. */
-enum { VRT_OPT_OCTANT_FIELDS = 1 /* 1 (default) = eight direction-octant radius fields, 0 = one isotropic field */ };
+enum {
+  VRT_OPT_OCTANT_FIELDS = 1, /* 1 (default) = eight direction-octant radius fields, 0 = one isotropic field */
+  VRT_OPT_RADIUS_CAP = 2     /* 1..255 = cap of the stored empty radius, 0 (default) = 255 up to 256^3, 96 above (build time is O(radius) per voxel) */
+};
 int vrt_set_option(vrt_ctx* ctx, int option, int value);
 
 /* ---- memory helpers for callers without a CUDA toolchain (ctypes, cgo ...) ---- */

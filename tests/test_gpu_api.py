@@ -94,3 +94,20 @@ def test_two_contexts_are_independent():
     assert not np.array_equal(f1, f2)
     assert np.array_equal(gpu_render(c1, p1, flags_extra=0).rgba8, f1)
     c1.close(); c2.close()
+
+
+def test_non_finite_uniforms_are_refused(ctx):
+    grid, n, atlas, ts = scene("glass_cube32")
+    ctx.upload_grid(grid, n); ctx.upload_atlas(atlas, ts)
+    for field in ("invPV", "sunDir", "time", "maxRayLength"):
+        p = make_params(64, 64, "glass_cube32", "start", vrt.FLAG_COLOR_ONLY)
+        if field == "invPV":
+            p.invPV[5] = float("nan")
+        elif field == "sunDir":
+            p.sunDir[1] = float("inf")
+        else:
+            setattr(p, field, float("nan"))
+        with pytest.raises(vrt.VrtError) as e:
+            ctx.render(p)
+        assert e.value.code == -1, field          # VRT_E_INVALID, and the context stays usable
+    assert gpu_render(ctx, make_params(64, 64, "glass_cube32", "start", vrt.FLAG_COLOR_ONLY), flags_extra=0).rgba8.shape == (4096, 4)

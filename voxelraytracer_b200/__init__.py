@@ -18,6 +18,7 @@ from .api import (  # noqa: F401
     FLAG_PERSISTENT,
     HIT_MISS,
     OPT_OCTANT_FIELDS,
+    OPT_RADIUS_CAP,
     Context,
     Counters,
     GridInfo,

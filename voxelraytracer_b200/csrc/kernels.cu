@@ -13,12 +13,6 @@ namespace vrt {
 #ifndef VRT_WARP_W
 #define VRT_WARP_W 8
 #endif
-#ifndef VRT_CTA_WX
-#define VRT_CTA_WX 4   // 4 x 1 warps of 8 x 4 pixels: a 32 x 4 patch whose rows are 128 bytes of RGBA8
-#endif
-#ifndef VRT_CTA_WY
-#define VRT_CTA_WY 1
-#endif
 #ifndef VRT_MIN_BLOCKS
 #define VRT_MIN_BLOCKS 12   // 40 registers, 48 warps/SM: the kernel is issue-bound and gains from more eligible warps (sweep2)
 #endif
@@ -28,9 +22,7 @@ namespace vrt {
 #define VRT_BOUNDS __launch_bounds__(kThreads)
 #endif
 constexpr int kWarpW = VRT_WARP_W, kWarpH = 32 / VRT_WARP_W;       // pixels per warp patch
-constexpr int kCtaWarpsX = VRT_CTA_WX, kCtaWarpsY = VRT_CTA_WY;
-constexpr int kCtaW = kWarpW * kCtaWarpsX, kCtaH = kWarpH * kCtaWarpsY;
-constexpr int kThreads = 32 * kCtaWarpsX * kCtaWarpsY;
+constexpr int kThreads = 128;                                      // 4 warps per CTA
 
 // Where pixel (lx, ly) of the tile goes in the colour target: compact tile rows, or its frame position (OUT_FRAME).
 __device__ __forceinline__ size_t colour_index(const FrameArgs& f, int lx, int ly) {
@@ -70,22 +62,27 @@ __device__ __forceinline__ void render_one(const FrameArgs& f, int lx, int ly, u
   }
 }
 
-template <class Tracer, bool FLAT, bool DEBUG>
+// WX x WY warps per CTA (always 4 warps = kThreads).  Two arrangements are instantiated:
+//   2 x 2 -> 16 x 8 pixel patch, 64-byte rows: best 2D locality, the default for frames in this GPU's own memory
+//            (+5 % at C5, +2 % at C4 over 4 x 1, equal at C2);
+//   4 x 1 -> 32 x 4 pixel patch, full 128-byte rows: what a REMOTE frame behind NVLink wants (8-GPU fused gather:
+//            0.102 ms per step instead of 0.112 with 64-byte and 0.143 with 32-byte row pieces).
+template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY>
 __global__ void VRT_BOUNDS render_kernel(const __grid_constant__ FrameArgs f) {
+  static_assert(WX * WY * 32 == kThreads, "4 warps per CTA");
+  constexpr int CW = kWarpW * WX, CH = kWarpH * WY;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int lx = blockIdx.x * kCtaW + (warp % kCtaWarpsX) * kWarpW + (lane & (kWarpW - 1));
-  const int ly = blockIdx.y * kCtaH + (warp / kCtaWarpsX) * kWarpH + (lane / kWarpW);
+  const int lx = blockIdx.x * CW + (warp % WX) * kWarpW + (lane & (kWarpW - 1));
+  const int ly = blockIdx.y * CH + (warp / WX) * kWarpH + (lane / kWarpW);
   // Rays are traced in 8x4 patches per warp (coherence), pixels are stored in rows: the CTA's patch goes through shared
-  // memory and each thread stores the pixel at (tid % kCtaW, tid / kCtaW), so that a warp writes whole 128-byte row
-  // segments.  That is what a remote frame (another GPU's memory behind NVLink, vrt_ipc_open) wants: at 8 GPUs the
-  // fused render+gather went from 0.143 to 0.105 ms per 1080p frame with full-row stores (profiles/).
-  __shared__ uchar4 patch[kCtaH][kCtaW];
+  // memory and each thread stores the pixel at (tid % CW, tid / CW), so that a warp writes whole row segments.
+  __shared__ uchar4 patch[CH][CW];
   uchar4 q = make_uchar4(0, 0, 0, 255);
   render_one<Tracer, FLAT, DEBUG, true>(f, lx, ly, &q);
-  patch[ly - blockIdx.y * kCtaH][lx - blockIdx.x * kCtaW] = q;
+  patch[ly - blockIdx.y * CH][lx - blockIdx.x * CW] = q;
   __syncthreads();
-  const int sx = threadIdx.x % kCtaW, sy = threadIdx.x / kCtaW;
-  const int ox = blockIdx.x * kCtaW + sx, oy = blockIdx.y * kCtaH + sy;
+  const int sx = threadIdx.x % CW, sy = threadIdx.x / CW;
+  const int ox = blockIdx.x * CW + sx, oy = blockIdx.y * CH + sy;
   if (ox < f.p.tile_w && oy < f.rows_local) reinterpret_cast<uchar4*>(f.out_rgba8)[colour_index(f, ox, oy)] = patch[sy][sx];
 }
 
@@ -126,21 +123,23 @@ cudaError_t launch_render_persistent(const FrameArgs& a, bool flat, unsigned int
   return launch_variant_persistent<FastTracer<false, false>, false, false>(a, ticket, num_sms, s);
 }
 
-template <class Tracer, bool FLAT, bool DEBUG>
+template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY>
 static cudaError_t launch_variant(const FrameArgs& a, cudaStream_t s) {
-  dim3 grid((unsigned)((a.p.tile_w + kCtaW - 1) / kCtaW), (unsigned)((a.rows_local + kCtaH - 1) / kCtaH));
+  constexpr int CW = kWarpW * WX, CH = kWarpH * WY;
+  dim3 grid((unsigned)((a.p.tile_w + CW - 1) / CW), (unsigned)((a.rows_local + CH - 1) / CH));
   if (grid.x == 0 || grid.y == 0) return cudaSuccess;
-  render_kernel<Tracer, FLAT, DEBUG><<<grid, kThreads, 0, s>>>(a);
+  render_kernel<Tracer, FLAT, DEBUG, WX, WY><<<grid, kThreads, 0, s>>>(a);
   return cudaGetLastError();
 }
 
-cudaError_t launch_render(const FrameArgs& a, bool exact, bool flat, bool debug, cudaStream_t s) {
+cudaError_t launch_render(const FrameArgs& a, bool exact, bool flat, bool debug, bool wide_rows, cudaStream_t s) {
   if (exact) {
-    if (flat) return debug ? launch_variant<ExactTracer<true, true>, true, true>(a, s) : launch_variant<ExactTracer<true, false>, true, false>(a, s);
-    return debug ? launch_variant<ExactTracer<false, true>, false, true>(a, s) : launch_variant<ExactTracer<false, false>, false, false>(a, s);
+    if (flat) return debug ? launch_variant<ExactTracer<true, true>, true, true, 2, 2>(a, s) : launch_variant<ExactTracer<true, false>, true, false, 2, 2>(a, s);
+    return debug ? launch_variant<ExactTracer<false, true>, false, true, 2, 2>(a, s) : launch_variant<ExactTracer<false, false>, false, false, 2, 2>(a, s);
   }
-  if (flat) return debug ? launch_variant<FastTracer<true, true>, true, true>(a, s) : launch_variant<FastTracer<true, false>, true, false>(a, s);
-  return debug ? launch_variant<FastTracer<false, true>, false, true>(a, s) : launch_variant<FastTracer<false, false>, false, false>(a, s);
+  if (debug) return flat ? launch_variant<FastTracer<true, true>, true, true, 2, 2>(a, s) : launch_variant<FastTracer<false, true>, false, true, 2, 2>(a, s);
+  if (wide_rows) return flat ? launch_variant<FastTracer<true, false>, true, false, 4, 1>(a, s) : launch_variant<FastTracer<false, false>, false, false, 4, 1>(a, s);
+  return flat ? launch_variant<FastTracer<true, false>, true, false, 2, 2>(a, s) : launch_variant<FastTracer<false, false>, false, false, 2, 2>(a, s);
 }
 
 }  // namespace vrt

@@ -4,6 +4,7 @@
 // without a CUDA device vrt_create() returns VRT_E_NO_DEVICE.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -24,6 +25,8 @@ struct vrt_ctx {
   uint16_t* d_cells = nullptr;     // (n+2)^3 traversal cells, x 8 with octant fields
   int opt_octants = 1;             // VRT_OPT_OCTANT_FIELDS (applies to the next upload)
   int octants = 0;                 // what d_cells holds
+  int opt_radius_cap = 0;          // VRT_OPT_RADIUS_CAP, 0 = default by chunk size
+  const void* tgt_ptr[8] = {nullptr}; bool tgt_remote[8] = {false}; int tgt_next = 0;   // remote_target() cache
   // atlas
   uint8_t* d_atlas = nullptr;
   int atlasSize = 0, atlasTextureSize = 0;
@@ -132,7 +135,7 @@ static int repack_locked(vrt_ctx* ctx, int size, cudaStream_t s) {
   cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * 8, s);
   int launches = 0;
   // Radius cap: 255 fits the byte; for big chunks a smaller cap bounds the build time (O(radius) per voxel).
-  const int cap = size <= 256 ? 255 : 96;
+  const int cap = ctx->opt_radius_cap > 0 ? ctx->opt_radius_cap : (size <= 256 ? 255 : 96);
   cudaError_t e = oct ? launch_repack_octants(ctx->d_grid, size, cap, tmp, tmp + n3, tmp + 2 * n3, ctx->d_cells, ctx->d_stats, s, &launches)
                       : launch_repack(ctx->d_grid, size, cap, tmp, tmp + n3, ctx->d_cells, ctx->d_stats, s, &launches);
   ctx->launches += launches;
@@ -206,12 +209,31 @@ static int validate(vrt_ctx* ctx, const vrt_params* p) {
     return fail(ctx, VRT_E_INVALID, "render: band_rows %d band_count %d band_index %d", p->band_rows, p->band_count, p->band_index);
   if (p->maxReflections < 0 || p->maxTransparencies < 0 || p->maxReflections + p->maxTransparencies > 7)
     return fail(ctx, VRT_E_INVALID, "render: maxReflections %d + maxTransparencies %d must be in [0,7]", p->maxReflections, p->maxTransparencies);
+  // Non-finite uniforms would turn into garbage cell indices on the device (float -> int of a NaN); refuse them here.
+  bool finite = std::isfinite(p->time) && std::isfinite(p->rayNoise) && std::isfinite(p->reflectionNoise) && std::isfinite(p->refractionNoise) &&
+                std::isfinite(p->maxRayLength) && std::isfinite(p->sunDir[0]) && std::isfinite(p->sunDir[1]) && std::isfinite(p->sunDir[2]);
+  for (int i = 0; i < 16; i++) finite = finite && std::isfinite(p->invPV[i]);
+  if (!finite) return fail(ctx, VRT_E_INVALID, "render: non-finite value in vrt_params (invPV / sunDir / noise / time / maxRayLength)");
   if (!(p->flags & VRT_FLAG_COLOR_ONLY)) {
     if (!ctx->d_atlas) return fail(ctx, VRT_E_NOT_READY, "render: textured shading needs an atlas (vrt_upload_atlas) or VRT_FLAG_COLOR_ONLY");
     if (p->atlasSize != ctx->atlasSize || p->atlasTextureSize != ctx->atlasTextureSize)
       return fail(ctx, VRT_E_INVALID, "render: params atlas %d/%d != uploaded atlas %d/%d", p->atlasSize, p->atlasTextureSize, ctx->atlasSize, ctx->atlasTextureSize);
   }
   return VRT_OK;
+}
+
+// True when `d_out` lives in another device's memory (a peer allocation or a CUDA IPC mapping): the render kernel then
+// uses the arrangement that stores full 128-byte rows.  Looked up once per distinct pointer.
+static bool remote_target(vrt_ctx* ctx, const void* d_out) {
+  if (!d_out || d_out == ctx->d_fb) return false;
+  for (int i = 0; i < 8; i++)
+    if (ctx->tgt_ptr[i] == d_out) return ctx->tgt_remote[i];
+  cudaPointerAttributes at;
+  bool remote = false;
+  if (cudaPointerGetAttributes(&at, d_out) == cudaSuccess) remote = at.type == cudaMemoryTypeDevice && at.device != ctx->device;
+  else cudaGetLastError();
+  ctx->tgt_ptr[ctx->tgt_next] = d_out; ctx->tgt_remote[ctx->tgt_next] = remote; ctx->tgt_next = (ctx->tgt_next + 1) & 7;
+  return remote;
 }
 
 static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaStream_t s) {
@@ -248,7 +270,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   if ((p->flags & VRT_FLAG_PERSISTENT) && !debug && !(p->flags & VRT_FLAG_EXACT)) {
     CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, (unsigned int*)(ctx->d_stats + 4), ctx->num_sms, s));
   } else {
-    CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, s));
+    CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, remote_target(ctx, d_out), s));
   }
   CU(cudaEventRecord(ctx->ev1, s));
   ctx->launches += 1;
@@ -369,6 +391,9 @@ int vrt_set_option(vrt_ctx* ctx, int option, int value) {
   if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_set_option: NULL ctx");
   switch (option) {
     case VRT_OPT_OCTANT_FIELDS: ctx->opt_octants = value ? 1 : 0; return VRT_OK;
+    case VRT_OPT_RADIUS_CAP:
+      if (value < 0 || value > 255) return fail(ctx, VRT_E_INVALID, "vrt_set_option: radius cap %d not in [0,255]", value);
+      ctx->opt_radius_cap = value; return VRT_OK;
     default: return fail(ctx, VRT_E_INVALID, "vrt_set_option: unknown option %d", option);
   }
 }
