@@ -291,17 +291,34 @@ def run_ours(args):
     gathered = None
     p2p_base = None
     if gather == "p2p":
-        # rank 0 owns the gathered frames (double-buffered); the others map them through CUDA IPC and store into them
-        if rank == 0:
-            p2p_base, handle = ctx.ipc_alloc_frame(2 * slots * frame_bytes)
-            box = [handle]
-        else:
-            box = [None]
+        # rank 0 owns the gathered frames (double-buffered); the others map them through CUDA IPC and store into them.
+        # If the mapping fails on any rank (no peer access between the devices), every rank falls back to the NCCL gather.
+        ok = 1
+        try:
+            if rank == 0:
+                p2p_base, handle = ctx.ipc_alloc_frame(2 * slots * frame_bytes)
+                box = [handle]
+            else:
+                box = [None]
+        except vrt.VrtError as e:
+            print("bench: ipc_alloc_frame failed: %s" % e, file=sys.stderr)
+            box, ok = [None], 0
         dist.broadcast_object_list(box, src=0)
-        if rank != 0:
-            p2p_base = ctx.ipc_open(box[0])
-        p2p_base = int(p2p_base.value)
-    elif gather == "nccl":
+        if rank != 0 and box[0] is not None:
+            try:
+                p2p_base = ctx.ipc_open(box[0])
+            except vrt.VrtError as e:
+                print("bench: ipc_open failed on rank %d: %s" % (rank, e), file=sys.stderr)
+                ok = 0
+        if box[0] is None:
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 1:
+            p2p_base = int(p2p_base.value)
+        else:
+            gather, p2p_base = "nccl", None
+    if gather == "nccl":
         per = sharding.max_rows(H, world, BR) * W * 4 if strong else frame_bytes
         gathered = torch.empty(world * per, dtype=torch.uint8, device="cuda")
         local_fb = [torch.zeros(per, dtype=torch.uint8, device="cuda") for _ in range(2)]

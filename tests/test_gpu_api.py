@@ -111,3 +111,29 @@ def test_non_finite_uniforms_are_refused(ctx):
             ctx.render(p)
         assert e.value.code == -1, field          # VRT_E_INVALID, and the context stays usable
     assert gpu_render(ctx, make_params(64, 64, "glass_cube32", "start", vrt.FLAG_COLOR_ONLY), flags_extra=0).rgba8.shape == (4096, 4)
+
+
+def test_async_host_copy_and_radius_cap_option(ctx):
+    """vrt_copy_to_host_async (double-buffered host read-back) and VRT_OPT_RADIUS_CAP (smaller cap = same pixels)."""
+    grid, n, atlas, ts = scene("glass_cube32")
+    ctx.upload_grid(grid, n); ctx.upload_atlas(atlas, ts)
+    p = make_params(200, 120, "glass_cube32", "start", vrt.FLAG_COLOR_ONLY)
+    want = gpu_render(ctx, p, flags_extra=0).rgba8
+    d = ctx.device_alloc(200 * 120 * 4)
+    host, hp = ctx.host_alloc(200 * 120 * 4)
+    host[:] = 0
+    ctx.render_to(p, d, None)
+    ctx.copy_to_host_async(hp, d, 200 * 120 * 4, None)
+    ctx.synchronize()
+    assert np.array_equal(host.reshape(-1, 4), want)
+    ctx.device_free(d)
+    try:
+        ctx.set_option(vrt.OPT_RADIUS_CAP, 3)
+        ctx.upload_grid(grid, n)
+        assert ctx.grid_info().radius_cap == 3 and int((ctx.read_cells() >> 8).max()) == 3
+        assert np.array_equal(gpu_render(ctx, p, flags_extra=0).rgba8, want)      # shorter jumps, same cells visited
+        with pytest.raises(vrt.VrtError):
+            ctx.set_option(vrt.OPT_RADIUS_CAP, 999)
+    finally:
+        ctx.set_option(vrt.OPT_RADIUS_CAP, 0)
+        ctx.upload_grid(grid, n)
