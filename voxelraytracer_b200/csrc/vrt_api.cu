@@ -127,11 +127,26 @@ int vrt_destroy(vrt_ctx* ctx) {
 
 static int repack_locked(vrt_ctx* ctx, int size, cudaStream_t s) {
   const size_t n3 = (size_t)size * size * size, p3 = (size_t)(size + 2) * (size + 2) * (size + 2);
-  const int oct = ctx->opt_octants ? 1 : 0;
+  int oct = ctx->opt_octants ? 1 : 0;
   if (ctx->d_cells) { cudaFree(ctx->d_cells); ctx->d_cells = nullptr; }
-  CU(cudaMalloc((void**)&ctx->d_cells, p3 * sizeof(uint16_t) * (oct ? 8 : 1)));
   uint8_t* tmp = nullptr;                                  // 2 (isotropic) or 3 (octants) scratch volumes of n^3 bytes
-  CU(cudaMalloc((void**)&tmp, n3 * (oct ? 3 : 2)));
+  if (oct) {
+    // eight fields need 16 (n+2)^3 + 3 n^3 bytes at once (163 GB at 2048^3): if that does not fit, build the single
+    // isotropic field instead of failing the upload
+    cudaError_t e1 = cudaMalloc((void**)&ctx->d_cells, p3 * sizeof(uint16_t) * 8);
+    cudaError_t e2 = e1 == cudaSuccess ? cudaMalloc((void**)&tmp, n3 * 3) : e1;
+    if (e1 != cudaSuccess || e2 != cudaSuccess) {
+      cudaGetLastError();
+      if (ctx->d_cells) { cudaFree(ctx->d_cells); ctx->d_cells = nullptr; }
+      tmp = nullptr;
+      oct = 0;
+    }
+  }
+  if (!oct) {
+    CU(cudaMalloc((void**)&ctx->d_cells, p3 * sizeof(uint16_t)));
+    cudaError_t e3 = cudaMalloc((void**)&tmp, n3 * 2);
+    if (e3 != cudaSuccess) { cudaFree(ctx->d_cells); ctx->d_cells = nullptr; return fail(ctx, VRT_E_OOM, "repack scratch: %s", cudaGetErrorString(e3)); }
+  }
   cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * 8, s);
   int launches = 0;
   // Radius cap: 255 fits the byte; for big chunks a smaller cap bounds the build time (O(radius) per voxel).
