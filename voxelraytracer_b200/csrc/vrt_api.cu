@@ -27,6 +27,7 @@ struct vrt_ctx {
   int octants = 0;                 // what d_cells holds
   int opt_radius_cap = 0;          // VRT_OPT_RADIUS_CAP, 0 = default by chunk size
   const void* tgt_ptr[8] = {nullptr}; bool tgt_remote[8] = {false}; int tgt_next = 0;   // remote_target() cache
+  uintptr_t ipc_lo[8] = {0}, ipc_hi[8] = {0}; int ipc_n = 0;                           // address ranges mapped by vrt_ipc_open
   // atlas
   uint8_t* d_atlas = nullptr;
   int atlasSize = 0, atlasTextureSize = 0;
@@ -241,6 +242,9 @@ static int validate(vrt_ctx* ctx, const vrt_params* p) {
 // uses the arrangement that stores full 128-byte rows.  Looked up once per distinct pointer.
 static bool remote_target(vrt_ctx* ctx, const void* d_out) {
   if (!d_out || d_out == ctx->d_fb) return false;
+  const uintptr_t a = (uintptr_t)d_out;
+  for (int i = 0; i < ctx->ipc_n; i++)
+    if (a >= ctx->ipc_lo[i] && a < ctx->ipc_hi[i]) return true;          // mapped from another process' (GPU's) allocation
   for (int i = 0; i < 8; i++)
     if (ctx->tgt_ptr[i] == d_out) return ctx->tgt_remote[i];
   cudaPointerAttributes at;
@@ -249,6 +253,19 @@ static bool remote_target(vrt_ctx* ctx, const void* d_out) {
   else cudaGetLastError();
   ctx->tgt_ptr[ctx->tgt_next] = d_out; ctx->tgt_remote[ctx->tgt_next] = remote; ctx->tgt_next = (ctx->tgt_next + 1) & 7;
   return remote;
+}
+
+// Size of the allocation behind an IPC mapping, through the driver entry point (libvrt links cudart statically and
+// libcuda not at all).  0 if it cannot be found out.
+static size_t mapped_range(const void* p, uintptr_t* base) {
+  typedef int (*range_fn)(unsigned long long*, size_t*, unsigned long long);
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qr;
+  if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn) { cudaGetLastError(); return 0; }
+  unsigned long long b = 0; size_t n = 0;
+  if (((range_fn)fn)(&b, &n, (unsigned long long)(uintptr_t)p) != 0) return 0;
+  *base = (uintptr_t)b;
+  return n;
 }
 
 static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaStream_t s) {
@@ -517,6 +534,13 @@ int vrt_ipc_open(vrt_ctx* ctx, const uint8_t handle[VRT_IPC_HANDLE_BYTES], void*
   cudaIpcMemHandle_t h;
   memcpy(&h, handle, sizeof(h));
   CU(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  if (ctx->ipc_n < 8) {
+    uintptr_t base = (uintptr_t)*d_ptr;
+    size_t n = mapped_range(*d_ptr, &base);
+    ctx->ipc_lo[ctx->ipc_n] = base;
+    ctx->ipc_hi[ctx->ipc_n] = n ? base + n : base + 1;     // unknown size: only the base pointer itself counts as remote
+    ctx->ipc_n++;
+  }
   return VRT_OK;
 }
 
@@ -524,7 +548,14 @@ int vrt_ipc_close(vrt_ctx* ctx, void* d_ptr) {
   if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_ipc_close: NULL ctx");
   int rc = bind(ctx);
   if (rc) return rc;
-  if (d_ptr) CU(cudaIpcCloseMemHandle(d_ptr));
+  if (d_ptr) {
+    for (int i = 0; i < ctx->ipc_n; i++)
+      if ((uintptr_t)d_ptr >= ctx->ipc_lo[i] && (uintptr_t)d_ptr < ctx->ipc_hi[i]) {
+        ctx->ipc_lo[i] = ctx->ipc_lo[ctx->ipc_n - 1]; ctx->ipc_hi[i] = ctx->ipc_hi[ctx->ipc_n - 1]; ctx->ipc_n--;
+        break;
+      }
+    CU(cudaIpcCloseMemHandle(d_ptr));
+  }
   return VRT_OK;
 }
 
