@@ -102,7 +102,8 @@ int vrt_destroy(vrt_ctx* ctx);
 const char* vrt_last_error(const vrt_ctx* ctx); /* never NULL; ctx may be NULL (global last error) */
 
 /* Replaces glTexImage3D(GL_TEXTURE_3D, GL_RED, size^3, GL_UNSIGNED_BYTE) (main.cpp:315-318).
- * voxels[x + y*size + z*size*size] (main.cpp:227); copied; size must be a power of two, 8..2048.
+ * voxels[x + y*size + z*size*size] (main.cpp:227); copied; size must be a power of two, 8..1024
+ * (cell indices are 32-bit: (size+2)^3 must stay below 2^32).
  * Triggers the on-device brick/occupancy repack. */
 int vrt_upload_grid(vrt_ctx* ctx, const uint8_t* voxels, int size);
 /* Same, with the grid already in device memory (e.g. filled by another kernel or broadcast by NCCL). */

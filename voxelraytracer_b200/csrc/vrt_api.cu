@@ -132,7 +132,7 @@ static int repack_locked(vrt_ctx* ctx, int size, cudaStream_t s) {
   if (ctx->d_cells) { cudaFree(ctx->d_cells); ctx->d_cells = nullptr; }
   uint8_t* tmp = nullptr;                                  // 2 (isotropic) or 3 (octants) scratch volumes of n^3 bytes
   if (oct) {
-    // eight fields need 16 (n+2)^3 + 3 n^3 bytes at once (163 GB at 2048^3): if that does not fit, build the single
+    // eight fields need 16 (n+2)^3 + 3 n^3 bytes at once (20 GB at 1024^3): if that does not fit, build the single
     // isotropic field instead of failing the upload
     cudaError_t e1 = cudaMalloc((void**)&ctx->d_cells, p3 * sizeof(uint16_t) * 8);
     cudaError_t e2 = e1 == cudaSuccess ? cudaMalloc((void**)&tmp, n3 * 3) : e1;
@@ -171,8 +171,8 @@ static int repack_locked(vrt_ctx* ctx, int size, cudaStream_t s) {
 }
 
 static int check_size(vrt_ctx* ctx, int size) {
-  if (size < 8 || size > 2048 || (size & (size - 1)) != 0)
-    return fail(ctx, VRT_E_INVALID, "grid size %d: must be a power of two in [8, 2048]", size);
+  if (size < 8 || size > 1024 || (size & (size - 1)) != 0)   // 32-bit cell indices: (size + 2)^3 < 2^32
+    return fail(ctx, VRT_E_INVALID, "grid size %d: must be a power of two in [8, 1024]", size);
   return VRT_OK;
 }
 
