@@ -215,6 +215,9 @@ int vrt_atlas_pack(const uint8_t* stone, const uint8_t* dirt, const uint8_t* gla
  * P = Perspective(aspect, fovDeg, near, far).  Angles in radians.  out: 16 floats, column-major. */
 int vrt_camera_invpv(const float pos[3], const float rot[3], float aspect, float fov_deg, float z_near, float z_far,
                      float out_invPV[16]);
+/* Frame export, the stand-in for Utils::Screenshot (main.cpp:423-429): 8-bit RGB PNG (alpha dropped, like the reference's
+ * RGB colour attachment).  gl_row_order != 0: row 0 of the buffer is the bottom scanline (what the render calls produce). */
+int vrt_write_png(const char* path, const uint8_t* rgba8, int width, int height, int gl_row_order);
 /* Sun direction from the day/night cycle (main.cpp:346-348). */
 int vrt_sun_dir(float timeOfDay, float dayTime, float out[3]);
 

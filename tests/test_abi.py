@@ -121,3 +121,16 @@ def test_atlas_layout():
     s = vrt.atlas_synthetic(16)
     glass = s[:16, :16]                      # bottom-left in memory = image bottom-left = glass
     assert (glass[0, :, 3] == 255).all() and glass[8, 8, 3] == 0   # opaque frame, clear interior (like res/textures/glass.png)
+
+
+def test_png_export_round_trips(tmp_path):
+    """vrt_write_png (stand-in for Utils::Screenshot, main.cpp:423-429): stored-deflate PNG that a stock decoder reads back."""
+    import numpy as np
+    Image = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(5)
+    for (w, h) in ((1, 1), (517, 300), (400, 400)):          # 517*300*3 > 65535: several stored blocks
+        a = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        path = tmp_path / ("f%dx%d.png" % (w, h))
+        vrt.write_png(path, a, w, h)
+        im = np.asarray(Image.open(path).convert("RGB"))
+        assert np.array_equal(im, a[::-1, :, :3])            # GL row order flipped to top-down, alpha dropped

@@ -34,6 +34,7 @@ from .api import (  # noqa: F401
     scene_fill,
     sun_dir,
     tile_pixels,
+    write_png,
 )
 from .build import build_library  # noqa: F401
 from .sharding import band_params, stitch_bands  # noqa: F401

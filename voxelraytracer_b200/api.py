@@ -27,7 +27,7 @@ EXPORTS = [
     "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells", "vrt_set_option",
     "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_host_async", "vrt_copy_to_device", "vrt_temporal_blend", "vrt_temporal_filter",
     "vrt_ipc_alloc_frame", "vrt_ipc_open", "vrt_ipc_close", "vrt_scene_fill", "vrt_noise_heightmap", "vrt_atlas_synthetic",
-    "vrt_atlas_pack", "vrt_camera_invpv", "vrt_sun_dir",
+    "vrt_atlas_pack", "vrt_camera_invpv", "vrt_sun_dir", "vrt_write_png",
 ]
 
 
@@ -133,6 +133,7 @@ def load_library():
         "vrt_atlas_pack": (i32, [vp, vp, vp, vp, i32, vp]),
         "vrt_camera_invpv": (i32, [C.POINTER(f32), C.POINTER(f32), f32, f32, f32, f32, C.POINTER(f32)]),
         "vrt_sun_dir": (i32, [f32, f32, C.POINTER(f32)]),
+        "vrt_write_png": (i32, [C.c_char_p, vp, i32, i32, i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)  # AttributeError here == header/library mismatch
@@ -203,6 +204,12 @@ def camera_invpv(pos, rot, aspect, fov_deg=90.0, z_near=0.01, z_far=100.0):
     _host_check(load_library().vrt_camera_invpv((C.c_float * 3)(*pos), (C.c_float * 3)(*rot), aspect, fov_deg, z_near, z_far, out),
                 "vrt_camera_invpv")
     return np.array(out, np.float32)
+
+
+def write_png(path, rgba8, width, height, gl_row_order=True):
+    """RGBA8 frame (as the render calls return it) -> 8-bit RGB PNG."""
+    a = np.ascontiguousarray(rgba8, np.uint8).reshape(height, width, 4)
+    _host_check(load_library().vrt_write_png(str(path).encode(), _ptr(a), width, height, 1 if gl_row_order else 0), "vrt_write_png")
 
 
 def sun_dir(time_of_day=0.0, day_time=50.0):

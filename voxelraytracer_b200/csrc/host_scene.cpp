@@ -8,6 +8,7 @@
 
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
 #include <cstring>
 #include <vector>
 
@@ -233,6 +234,60 @@ int vrt_camera_invpv(const float pos[3], const float rot[3], float aspect, float
   if (!mat_inv(PV, I)) return VRT_E_INVALID;  // invPV = ~(P * V) (main.cpp:75)
   for (int i = 0; i < 16; i++) out[i] = (float)I[i];
   return VRT_OK;
+}
+
+// ---- frame export (the reference's only file output is Utils::Screenshot, main.cpp:423-429) ----
+// Minimal PNG writer: 8-bit RGB, filter 0 on every scanline, zlib stream of stored (uncompressed) deflate blocks.
+namespace {
+uint32_t crc_table_entry(uint32_t n) { for (int k = 0; k < 8; k++) n = (n & 1u) ? 0xEDB88320u ^ (n >> 1) : n >> 1; return n; }
+uint32_t crc32_update(uint32_t c, const uint8_t* p, size_t n) {
+  static uint32_t table[256]; static bool init = false;
+  if (!init) { for (uint32_t i = 0; i < 256; i++) table[i] = crc_table_entry(i); init = true; }
+  for (size_t i = 0; i < n; i++) c = table[(c ^ p[i]) & 0xFFu] ^ (c >> 8);
+  return c;
+}
+void put32(std::vector<uint8_t>& v, uint32_t x) { v.push_back(x >> 24); v.push_back(x >> 16); v.push_back(x >> 8); v.push_back(x); }
+void chunk(std::vector<uint8_t>& out, const char type[4], const std::vector<uint8_t>& data) {
+  put32(out, (uint32_t)data.size());
+  std::vector<uint8_t> td(type, type + 4);
+  td.insert(td.end(), data.begin(), data.end());
+  out.insert(out.end(), td.begin(), td.end());
+  put32(out, crc32_update(0xFFFFFFFFu, td.data(), td.size()) ^ 0xFFFFFFFFu);
+}
+}  // namespace
+
+int vrt_write_png(const char* path, const uint8_t* rgba8, int width, int height, int gl_row_order) {
+  if (!path || !rgba8 || width < 1 || height < 1) return VRT_E_INVALID;
+  std::vector<uint8_t> raw;                                   // filter byte + RGB per scanline, top row first
+  raw.reserve((size_t)height * ((size_t)width * 3 + 1));
+  for (int y = 0; y < height; y++) {
+    const uint8_t* row = rgba8 + (size_t)(gl_row_order ? height - 1 - y : y) * width * 4;
+    raw.push_back(0);
+    for (int x = 0; x < width; x++) { raw.push_back(row[4 * x]); raw.push_back(row[4 * x + 1]); raw.push_back(row[4 * x + 2]); }
+  }
+  std::vector<uint8_t> z = {0x78, 0x01};                      // zlib header, then stored blocks of <= 65535 bytes
+  uint32_t a = 1, b = 0;                                      // Adler-32
+  for (size_t off = 0; off < raw.size();) {
+    size_t n = raw.size() - off < 65535 ? raw.size() - off : 65535;
+    z.push_back(off + n == raw.size() ? 1 : 0);
+    z.push_back(n & 0xFF); z.push_back(n >> 8); z.push_back(~n & 0xFF); z.push_back((~n >> 8) & 0xFF);
+    z.insert(z.end(), raw.begin() + off, raw.begin() + off + n);
+    for (size_t i = off; i < off + n; i++) { a = (a + raw[i]) % 65521u; b = (b + a) % 65521u; }
+    off += n;
+  }
+  put32(z, (b << 16) | a);
+  std::vector<uint8_t> out = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
+  std::vector<uint8_t> ihdr;
+  put32(ihdr, (uint32_t)width); put32(ihdr, (uint32_t)height);
+  ihdr.push_back(8); ihdr.push_back(2); ihdr.push_back(0); ihdr.push_back(0); ihdr.push_back(0);   // 8-bit RGB, no interlace
+  chunk(out, "IHDR", ihdr);
+  chunk(out, "IDAT", z);
+  chunk(out, "IEND", {});
+  FILE* f = std::fopen(path, "wb");
+  if (!f) return VRT_E_INVALID;
+  size_t w = std::fwrite(out.data(), 1, out.size(), f);
+  std::fclose(f);
+  return w == out.size() ? VRT_OK : VRT_E_INVALID;
 }
 
 int vrt_sun_dir(float timeOfDay, float dayTime, float out[3]) {

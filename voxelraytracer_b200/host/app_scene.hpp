@@ -114,7 +114,8 @@ class AppScene {
   uint32_t frame_counter_ = 0;
 };
 
-// Top-down PPM of a GL-ordered RGBA8 frame (the reference's screenshot is the only file output it has).
+// Top-down PPM of a GL-ordered RGBA8 frame (the reference's screenshot is the only file output it has); vrt_write_png
+// in the C ABI writes the same frame as a PNG.
 inline bool write_ppm(const char* path, const std::vector<uint8_t>& rgba, uint32_t w, uint32_t h) {
   FILE* f = std::fopen(path, "wb");
   if (!f) return false;

@@ -38,7 +38,10 @@ int main(int argc, char** argv) {
     for (uint8_t b : img) sum += b;
     std::printf("frames %d size %ux%u chunk %u^3 trace_ms_avg %.4f fps %.1f checksum %llu\n", frames, scene.lastFrameBuffer->GetWidth(),
                 scene.lastFrameBuffer->GetHeight(), scene.size, frames > 1 ? ms_sum / (frames - 1) : (double)scene.last_render_ms(), scene.fps, sum);
-    if (out && !write_ppm(out, img, scene.lastFrameBuffer->GetWidth(), scene.lastFrameBuffer->GetHeight())) { std::fprintf(stderr, "cannot write %s\n", out); return 1; }
+    const size_t ol = out ? std::strlen(out) : 0;
+    const bool png = ol > 4 && !std::strcmp(out + ol - 4, ".png");
+    if (out && !(png ? vrt_write_png(out, img.data(), (int)scene.lastFrameBuffer->GetWidth(), (int)scene.lastFrameBuffer->GetHeight(), 1) == VRT_OK
+                     : write_ppm(out, img, scene.lastFrameBuffer->GetWidth(), scene.lastFrameBuffer->GetHeight()))) { std::fprintf(stderr, "cannot write %s\n", out); return 1; }
   } catch (const Error& e) {
     std::fprintf(stderr, "vrt_demo: %s (code %d)\n", e.what(), e.code);
     return e.code == VRT_E_NO_DEVICE ? 2 : 1;
