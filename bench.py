@@ -81,6 +81,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--octants", type=int, default=1, choices=[0, 1], help="VRT_OPT_OCTANT_FIELDS (tuning comparison; 1 = default)")
     ap.add_argument("--radius-cap", type=int, default=0, help="VRT_OPT_RADIUS_CAP (tuning comparison; 0 = default)")
+    ap.add_argument("--e2e-depth", type=int, default=4, help="frames in flight in the overlapped e2e leg")
     ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
     return ap.parse_args()
 
@@ -489,44 +490,67 @@ def run_ours(args):
     #  overlapped: vrt_render_to + vrt_copy_to_host_async on two streams with two device/host buffers (two frames in flight), the
     #              double-buffered form a frame loop would use; every frame still lands in host memory inside the timed region
     host, hp = ctx.host_alloc(my_pix * 4)
-    for i in range(3):
-        ctx.render_host(frames[i % len(frames)], hp, stream.cuda_stream)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        ctx.render_host(frames[i % len(frames)], hp, stream.cuda_stream)
-    torch.cuda.synchronize()
-    t_e2e_sync = time.perf_counter() - t0
-    hosts = [ctx.host_alloc(my_pix * 4) for _ in range(2)]
-    dbuf = [torch.empty(my_pix * 4, dtype=torch.uint8, device="cuda") for _ in range(2)]
-    st2 = [torch.cuda.Stream(), torch.cuda.Stream()]
+
+    def sync_leg(direct):
+        ctx.set_option(vrt.OPT_HOST_DIRECT, direct)
+        for i in range(3):
+            ctx.render_host(frames[i % len(frames)], hp, stream.cuda_stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            ctx.render_host(frames[i % len(frames)], hp, stream.cuda_stream)
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0
+
+    t_sync_staged = sync_leg(0)                      # device frame, then a copy
+    t_e2e_sync = sync_leg(1)                         # the kernel stores into the pinned buffer (VRT_OPT_HOST_DIRECT, the default)
+    D = max(2, args.e2e_depth)                       # frames in flight
+    hosts = [ctx.host_alloc(my_pix * 4) for _ in range(D)]
+    dbuf = [torch.empty(my_pix * 4, dtype=torch.uint8, device="cuda") for _ in range(D)]
+    st2 = [torch.cuda.Stream() for _ in range(D)]
 
     def e2e_step(i):
-        st = st2[i % 2]
-        ctx.render_to(frames[i % len(frames)], dbuf[i % 2].data_ptr(), st.cuda_stream)
-        ctx.copy_to_host_async(hosts[i % 2][1], dbuf[i % 2].data_ptr(), my_pix * 4, st.cuda_stream)
+        st = st2[i % D]
+        ctx.render_to(frames[i % len(frames)], dbuf[i % D].data_ptr(), st.cuda_stream)
+        ctx.copy_to_host_async(hosts[i % D][1], dbuf[i % D].data_ptr(), my_pix * 4, st.cuda_stream)
 
-    for i in range(4):
-        e2e_step(i)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
+    def overlapped(step_fn):
+        for i in range(2 * D):
+            step_fn(i)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            if i >= D:
+                st2[i % D].synchronize()             # frame i-D is in host memory (a consumer would read it here)
+            step_fn(i)
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0
+
+    def e2e_direct(i):                               # no device frame, no copy: the render kernel's row stores cross PCIe
+        ctx.render_to(frames[i % len(frames)], hosts[i % D][1], st2[i % D].cuda_stream)
+
+    t_e2e_direct = overlapped(e2e_direct)
+    direct_ok = bool(np.array_equal(hosts[(args.steps - 1) % D][0], ctx_frame_host(ctx, frames[(args.steps - 1) % len(frames)], my_pix)))
+    t_e2e_staged = overlapped(e2e_step)
+    e2e_ok = bool(np.array_equal(hosts[(args.steps - 1) % D][0], dbuf[(args.steps - 1) % D].cpu().numpy())) and direct_ok
+    # the bound of the overlapped form: the same loop with the render left out (device -> pinned host copies only)
     t0 = time.perf_counter()
     for i in range(args.steps):
-        if i >= 2:
-            st2[i % 2].synchronize()                 # frame i-2 is in host memory (a consumer would read it here)
-        e2e_step(i)
+        if i >= D:
+            st2[i % D].synchronize()
+        ctx.copy_to_host_async(hosts[i % D][1], dbuf[i % D].data_ptr(), my_pix * 4, st2[i % D].cuda_stream)
     torch.cuda.synchronize()
-    t_e2e = time.perf_counter() - t0
-    e2e_ok = bool(np.array_equal(hosts[(args.steps - 1) % 2][0], dbuf[(args.steps - 1) % 2].cpu().numpy()))
+    t_copy = time.perf_counter() - t0
 
     # max over ranks for times, sum over ranks for work
     if world > 1:
-        v = torch.tensor([t_steps, t_kernel, t_e2e, t_pipeline or 0.0, t_e2e_sync], dtype=torch.float64, device="cuda")
+        v = torch.tensor([t_steps, t_kernel, t_e2e_direct, t_pipeline or 0.0, t_e2e_sync, t_e2e_staged, t_sync_staged], dtype=torch.float64, device="cuda")
         dist.all_reduce(v, op=dist.ReduceOp.MAX)
-        t_step_total, t_kernel_max, t_e2e, t_pipeline, t_e2e_sync = [float(x) for x in v.cpu()]
+        t_step_total, t_kernel_max, t_e2e_direct, t_pipeline, t_e2e_sync, t_e2e_staged, t_sync_staged = [float(x) for x in v.cpu()]
         s = torch.tensor([rays, steps_ref, steps_act, hits], dtype=torch.float64, device="cuda")
         dist.all_reduce(s, op=dist.ReduceOp.SUM)
         rays_all, steps_all, act_all, hits_all = [float(x) for x in s.cpu()]
@@ -534,6 +558,7 @@ def run_ours(args):
         t_step_total, t_kernel_max = t_steps, t_kernel
         rays_all, steps_all, act_all, hits_all = float(rays), float(steps_ref), float(steps_act), float(hits)
 
+    t_e2e = min(t_e2e_direct, t_e2e_staged)
     if rank == 0:
         peaks = {}
         try:
@@ -575,9 +600,17 @@ def run_ours(args):
                              "frac": bytes_per_launch / per_launch_s / 1e9 / hbm_peak, "traffic": NCU_TRAFFIC.get(args.workload),
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"},
             "e2e": {"value": rays_all / t_e2e / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(vrt.Params), "d2h_bytes_per_step": my_pix * 4,
-                    "call": "vrt_render_to + vrt_copy_to_host_async, two frames in flight (params by value, RGBA8 pixels into pinned host memory every step), per rank",
-                    "sync_value": rays_all / t_e2e_sync / 1e6, "sync_call": "vrt_render_host: render, copy, synchronise, one frame at a time",
-                    "host_frame_check": e2e_ok},
+                    "call": ("vrt_render_to into pinned host memory (the render kernel's 128-byte row stores cross PCIe; no device frame, no copy)"
+                             if t_e2e_direct <= t_e2e_staged else "vrt_render_to + vrt_copy_to_host_async")
+                            + ", %d frames in flight on %d streams (params by value, RGBA8 pixels in pinned host memory every step), per rank" % (D, D),
+                    "direct_value": rays_all / t_e2e_direct / 1e6, "staged_value": rays_all / t_e2e_staged / 1e6,
+                    "staged_call": "vrt_render_to (device frame) + vrt_copy_to_host_async, same streams",
+                    "sync_value": rays_all / t_e2e_sync / 1e6,
+                    "sync_call": "vrt_render_host into pinned memory (kernel stores straight to the host), synchronised, one frame at a time",
+                    "sync_staged_value": rays_all / t_sync_staged / 1e6, "sync_staged_call": "vrt_render_host with VRT_OPT_HOST_DIRECT = 0: render, copy, synchronise",
+                    "host_frame_check": e2e_ok,
+                    "d2h_only_ms_per_step": 1e3 * t_copy / args.steps, "d2h_only_gbs": my_pix * 4 * args.steps / t_copy / 1e9,
+                    "frac_of_d2h_bound": t_copy / t_e2e if world == 1 else None},
             "gpu_launches": int(launches_timed),      # render_kernel launches of rank 0 inside the timed region (one per step)
             "gather_check": gather_check,
             "upload_grid_s": t_upload, "radius_fields": "8 direction-octant fields" if args.octants else "1 isotropic field",
@@ -595,6 +628,13 @@ def run_ours(args):
         dist.destroy_process_group()
     ctx.close()
     return 0
+
+
+def ctx_frame_host(ctx, p, npix):
+    """The same frame through vrt_render + vrt_read_framebuffer (device frame, blocking copy), as the check for the direct leg."""
+    ctx.render(p)
+    ctx.synchronize()
+    return ctx.read_framebuffer(p).reshape(-1)[:npix * 4]
 
 
 def _wrap_device(torch, ptr, nbytes):

@@ -117,10 +117,13 @@ int vrt_upload_atlas(vrt_ctx* ctx, const uint8_t* rgba8, int atlasSize, int text
  * tile).  Asynchronous on `stream`.  Output: RGBA8, tile rows compact, into the ctx-owned framebuffer
  * (grown on demand like FrameBuffer::Resize, FrameBuffer.cpp:47-60). */
 int vrt_render(vrt_ctx* ctx, const vrt_params* p, void* stream);
-/* Same, into caller-provided DEVICE memory (>= vrt_tile_pixels(p)*4 bytes): a torch tensor, or another
- * GPU's buffer mapped through P2P/IPC so that the frame is gathered by the render kernel's own stores. */
+/* Same, into caller-provided memory the device can address (>= vrt_tile_pixels(p)*4 bytes): a torch tensor, another
+ * GPU's buffer mapped through P2P/IPC so that the frame is gathered by the render kernel's own stores, or pinned host
+ * memory (vrt_host_alloc) so that the frame crosses PCIe while it is being rendered.  For targets outside this GPU's own
+ * memory the kernel arrangement that stores whole 128-byte rows is used. */
 int vrt_render_to(vrt_ctx* ctx, const vrt_params* p, void* d_rgba8, void* stream);
-/* Render + device->host copy + synchronise: what a host caller of the reference sees (frame in host memory). */
+/* Render + synchronise with the frame in host memory: what a host caller of the reference sees.  Pinned `host_rgba8`
+ * (vrt_host_alloc): the kernel stores into it directly (VRT_OPT_HOST_DIRECT); pageable: device frame, then a copy. */
 int vrt_render_host(vrt_ctx* ctx, const vrt_params* p, uint8_t* host_rgba8, void* stream);
 
 /* Number of pixels a render with these params writes (tile and band selection applied). */
@@ -160,10 +163,12 @@ typedef struct vrt_grid_info {
 int vrt_grid_info_get(vrt_ctx* ctx, vrt_grid_info* out);
 int vrt_read_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count); /* count must be cells_total */
 
-/* Tuning options; take effect at the next vrt_upload_grid. */
+/* Tuning options; 1 and 2 take effect at the next vrt_upload_grid, 3 at the next render. */
 enum {
   VRT_OPT_OCTANT_FIELDS = 1, /* 1 (default) = eight direction-octant radius fields, 0 = one isotropic field */
-  VRT_OPT_RADIUS_CAP = 2     /* 1..255 = cap of the stored empty radius, 0 (default) = 255 up to 256^3, 96 above (build time is O(radius) per voxel) */
+  VRT_OPT_RADIUS_CAP = 2,    /* 1..255 = cap of the stored empty radius, 0 (default) = 255 up to 256^3, 96 above (build time is O(radius) per voxel) */
+  VRT_OPT_HOST_DIRECT = 3    /* 1 (default) = vrt_render_host into PINNED host memory lets the render kernel store the pixels straight
+                                into it over PCIe (no device frame, no copy); 0 = always render to the device frame, then copy */
 };
 int vrt_set_option(vrt_ctx* ctx, int option, int value);
 

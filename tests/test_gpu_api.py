@@ -55,9 +55,26 @@ def test_render_to_torch_tensor_and_render_host(ctx):
     s.synchronize()
     assert np.array_equal(t.cpu().numpy().reshape(-1, 4), ref)
     host, hp = ctx.host_alloc(W * H * 4)
-    ctx.render_host(p, hp)
+    ctx.render_host(p, hp)                                     # pinned: the kernel stores straight into host memory
     assert np.array_equal(host.reshape(-1, 4), ref)
     assert ctx.last_render_ms() > 0.0
+    host[:] = 0
+    ctx.set_option(vrt.OPT_HOST_DIRECT, 0)                     # device frame + copy
+    ctx.render_host(p, hp)
+    ctx.set_option(vrt.OPT_HOST_DIRECT, 1)
+    assert np.array_equal(host.reshape(-1, 4), ref)
+    pageable = np.zeros(W * H * 4, np.uint8)                   # not pinned: falls back to the copy by itself
+    ctx.render_host(p, pageable.ctypes.data_as(C.c_void_p))
+    assert np.array_equal(pageable.reshape(-1, 4), ref)
+    # ragged frame straight into pinned memory through vrt_render_to (row-store arrangement, partial patches)
+    W2, H2 = 333, 77
+    p2 = make_params(W2, H2, "terrain32", "terrain32_above")
+    ref2 = gpu_render(ctx, p2, flags_extra=0).rgba8
+    host2, hp2 = ctx.host_alloc(W2 * H2 * 4 + 64)
+    host2[:] = 0xAB
+    ctx.render_to(p2, hp2); ctx.synchronize()
+    assert np.array_equal(host2[:W2 * H2 * 4].reshape(-1, 4), ref2)
+    assert (host2[W2 * H2 * 4:] == 0xAB).all()                 # nothing written past the frame
     before = ctx.kernel_launches()
     ctx.render(p); ctx.synchronize()
     assert ctx.kernel_launches() == before + 1

@@ -19,6 +19,7 @@ from .api import (  # noqa: F401
     HIT_MISS,
     OPT_OCTANT_FIELDS,
     OPT_RADIUS_CAP,
+    OPT_HOST_DIRECT,
     Context,
     Counters,
     GridInfo,

@@ -15,6 +15,7 @@ FLAG_OUT_FRAME = 0x20
 FLAG_PERSISTENT = 0x40
 OPT_OCTANT_FIELDS = 1
 OPT_RADIUS_CAP = 2
+OPT_HOST_DIRECT = 3
 HIT_MISS = 0xFFFFFFFF
 
 SCENE_TERRAIN, SCENE_GLASS_CUBE, SCENE_REFRACTION, SCENE_SYNTHETIC = 0, 1, 2, 3

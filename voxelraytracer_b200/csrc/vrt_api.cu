@@ -26,6 +26,7 @@ struct vrt_ctx {
   int opt_octants = 1;             // VRT_OPT_OCTANT_FIELDS (applies to the next upload)
   int octants = 0;                 // what d_cells holds
   int opt_radius_cap = 0;          // VRT_OPT_RADIUS_CAP, 0 = default by chunk size
+  int opt_host_direct = 1;         // VRT_OPT_HOST_DIRECT
   const void* tgt_ptr[8] = {nullptr}; bool tgt_remote[8] = {false}; int tgt_next = 0;   // remote_target() cache
   uintptr_t ipc_lo[8] = {0}, ipc_hi[8] = {0}; int ipc_n = 0;                           // address ranges mapped by vrt_ipc_open
   // atlas
@@ -238,8 +239,8 @@ static int validate(vrt_ctx* ctx, const vrt_params* p) {
   return VRT_OK;
 }
 
-// True when `d_out` lives in another device's memory (a peer allocation or a CUDA IPC mapping): the render kernel then
-// uses the arrangement that stores full 128-byte rows.  Looked up once per distinct pointer.
+// True when `d_out` lives outside this device's memory (a peer allocation, a CUDA IPC mapping, pinned host memory): the
+// render kernel then uses the arrangement that stores full 128-byte rows.  Looked up once per distinct pointer.
 static bool remote_target(vrt_ctx* ctx, const void* d_out) {
   if (!d_out || d_out == ctx->d_fb) return false;
   const uintptr_t a = (uintptr_t)d_out;
@@ -249,7 +250,7 @@ static bool remote_target(vrt_ctx* ctx, const void* d_out) {
     if (ctx->tgt_ptr[i] == d_out) return ctx->tgt_remote[i];
   cudaPointerAttributes at;
   bool remote = false;
-  if (cudaPointerGetAttributes(&at, d_out) == cudaSuccess) remote = at.type == cudaMemoryTypeDevice && at.device != ctx->device;
+  if (cudaPointerGetAttributes(&at, d_out) == cudaSuccess) remote = (at.type == cudaMemoryTypeDevice && at.device != ctx->device) || at.type == cudaMemoryTypeHost;
   else cudaGetLastError();
   ctx->tgt_ptr[ctx->tgt_next] = d_out; ctx->tgt_remote[ctx->tgt_next] = remote; ctx->tgt_next = (ctx->tgt_next + 1) & 7;
   return remote;
@@ -321,8 +322,19 @@ int vrt_render_to(vrt_ctx* ctx, const vrt_params* p, void* d_rgba8, void* stream
 
 int vrt_render_host(vrt_ctx* ctx, const vrt_params* p, uint8_t* host_rgba8, void* stream) {
   if (!host_rgba8) return fail(ctx, VRT_E_INVALID, "vrt_render_host: NULL output");
-  int rc = render_impl(ctx, p, nullptr, (cudaStream_t)stream);
-  if (rc) return rc;
+  int rc;
+  if (ctx && ctx->opt_host_direct && !(p && (p->flags & VRT_FLAG_OUT_FRAME))) {
+    if ((rc = bind(ctx))) return rc;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, host_rgba8) != cudaSuccess) { cudaGetLastError(); at.type = cudaMemoryTypeUnregistered; }
+    if (at.type == cudaMemoryTypeHost && at.devicePointer) {
+      // pinned: the kernel's row stores go over PCIe while the rest of the frame is still being traced
+      if ((rc = render_impl(ctx, p, (uint8_t*)at.devicePointer, (cudaStream_t)stream))) return rc;
+      CU(cudaStreamSynchronize((cudaStream_t)stream));
+      return VRT_OK;
+    }
+  }
+  if ((rc = render_impl(ctx, p, nullptr, (cudaStream_t)stream))) return rc;
   CU(cudaMemcpyAsync(host_rgba8, ctx->d_fb, (size_t)ctx->last_pixels * 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   CU(cudaStreamSynchronize((cudaStream_t)stream));
   return VRT_OK;
@@ -423,6 +435,7 @@ int vrt_set_option(vrt_ctx* ctx, int option, int value) {
   if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_set_option: NULL ctx");
   switch (option) {
     case VRT_OPT_OCTANT_FIELDS: ctx->opt_octants = value ? 1 : 0; return VRT_OK;
+    case VRT_OPT_HOST_DIRECT: ctx->opt_host_direct = value ? 1 : 0; return VRT_OK;
     case VRT_OPT_RADIUS_CAP:
       if (value < 0 || value > 255) return fail(ctx, VRT_E_INVALID, "vrt_set_option: radius cap %d not in [0,255]", value);
       ctx->opt_radius_cap = value; return VRT_OK;
