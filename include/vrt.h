@@ -50,6 +50,9 @@ enum {
 
 #define VRT_FLAG_PERSISTENT 0x40u /* tuning: persistent-warp launch (resident CTAs pull 8x4 patches from an atomic ticket)
                                      instead of one CTA per 16x8 patch; same pixels.  Ignored with EXACT / debug flags. */
+#define VRT_FLAG_RGB8_OUT   0x80u /* colour target is packed RGB8, 3 bytes per pixel, rows tight (the reference's colour attachment is
+                                   * TextureInternalFormat::RGB, FrameBuffer.cpp:8,53; glReadPixels(GL_RGB) layout): 25 % fewer bytes
+                                   * for a frame that leaves the GPU.  Every size below that says pixels*4 is pixels*3 then. */
 
 #define VRT_HIT_MISS 0xFFFFFFFFu
 

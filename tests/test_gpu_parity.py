@@ -192,6 +192,46 @@ def test_out_frame_flag_writes_bands_in_place(ctx):
         ctx.render(q)                                 # needs vrt_render_to
 
 
+def test_rgb8_output_is_the_rgba8_frame_without_alpha(ctx):
+    """VRT_FLAG_RGB8_OUT (the reference's colour attachment format, FrameBuffer.cpp:8): packed 3-byte pixels, every launch shape."""
+    from voxelraytracer_b200 import sharding
+    grid, n, atlas, ts = upload(ctx, "terrain32")
+    for W, H in ((320, 200), (333, 77), (17, 5), (1, 1)):          # word-aligned rows, ragged rows (byte stores), tiny
+        p = make_params(W, H, "terrain32", "terrain32_above")
+        rgba = gpu_render(ctx, p, flags_extra=0).rgba8.reshape(H, W, 4)
+        assert (rgba[..., 3] == 255).all()
+        rgb = gpu_render(ctx, p, flags_extra=vrt.FLAG_RGB8_OUT).rgba8                 # 2x2-warp arrangement, ctx-owned frame
+        assert rgb.shape == (W * H, 3) and np.array_equal(rgb.reshape(H, W, 3), rgba[..., :3])
+        # exact tracer and the debug kernels share the store stage
+        rgb = gpu_render(ctx, p, flags_extra=vrt.FLAG_RGB8_OUT | vrt.FLAG_EXACT | vrt.FLAG_DEBUG_MAPS).rgba8
+        ex = gpu_render(ctx, p, flags_extra=vrt.FLAG_EXACT).rgba8.reshape(H, W, 4)
+        assert np.array_equal(rgb.reshape(H, W, 3), ex[..., :3])
+        # 4x1-warp arrangement (row stores) straight into pinned host memory, with guard bytes either side
+        host, hp = ctx.host_alloc(W * H * 3 + 128)
+        host[:] = 0xCD
+        q = p.copy(); q.flags |= vrt.FLAG_RGB8_OUT
+        ctx.render_to(q, hp.value + 61, None); ctx.synchronize()                       # odd base address: byte-store path
+        assert np.array_equal(host[61:61 + W * H * 3].reshape(H, W, 3), rgba[..., :3])
+        assert (host[:61] == 0xCD).all() and (host[61 + W * H * 3:] == 0xCD).all()
+        host[:] = 0xCD
+        ctx.render_host(q, hp.value + 64)
+        assert np.array_equal(host[64:64 + W * H * 3].reshape(H, W, 3), rgba[..., :3])
+        assert (host[:64] == 0xCD).all() and (host[64 + W * H * 3:] == 0xCD).all()
+    # bands into one full frame
+    W, H = 322, 181
+    p = make_params(W, H, "terrain32", "terrain32_above")
+    full = gpu_render(ctx, p, flags_extra=0).rgba8.reshape(H, W, 4)[..., :3]
+    d = ctx.device_alloc(W * H * 3)
+    try:
+        for r in range(3):
+            q = sharding.band_params(p, r, 3, 16)
+            q.flags |= vrt.FLAG_OUT_FRAME | vrt.FLAG_RGB8_OUT
+            ctx.render_to(q, d, None)
+        assert np.array_equal(ctx.copy_to_host(d, W * H * 3).reshape(H, W, 3), full)
+    finally:
+        ctx.device_free(d)
+
+
 def test_persistent_launch_writes_the_same_pixels(ctx):
     for sc, pose, fl, W, H in (("terrain128", "terrain_low", 0, 1001, 563), ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY, 400, 400)):
         grid, n, atlas, ts = upload(ctx, sc)

@@ -13,6 +13,7 @@ FLAG_COUNTERS = 0x8
 FLAG_FLOAT_OUT = 0x10
 FLAG_OUT_FRAME = 0x20
 FLAG_PERSISTENT = 0x40
+FLAG_RGB8_OUT = 0x80
 OPT_OCTANT_FIELDS = 1
 OPT_RADIUS_CAP = 2
 OPT_HOST_DIRECT = 3
@@ -283,7 +284,7 @@ class Context:
 
     def read_framebuffer(self, p):
         n = tile_pixels(p)
-        out = np.zeros((n, 4), np.uint8)
+        out = np.zeros((n, 3 if p.flags & FLAG_RGB8_OUT else 4), np.uint8)
         self._check(self.lib.vrt_read_framebuffer(self.h, _ptr(out), out.nbytes))
         return out
 

@@ -83,6 +83,26 @@ __global__ void VRT_BOUNDS render_kernel(const __grid_constant__ FrameArgs f) {
   __syncthreads();
   const int sx = threadIdx.x % CW, sy = threadIdx.x / CW;
   const int ox = blockIdx.x * CW + sx, oy = blockIdx.y * CH + sy;
+  if (f.p.flags & VRT_FLAG_RGB8_OUT) {
+    // Packed RGB8: a patch row is CW*3 bytes = CW*3/4 words; thread sx composes word sx of the row from the patch bytes.
+    constexpr int WPR = CW * 3 / 4;
+    if (sx >= WPR || oy >= f.rows_local) return;
+    const int x0 = blockIdx.x * CW;                                                        // first pixel of the patch row
+    const int valid = (f.p.tile_w - x0 < CW ? f.p.tile_w - x0 : CW) * 3;                   // bytes of this row inside the tile
+    const uint8_t* pb = reinterpret_cast<const uint8_t*>(&patch[sy][0]);
+    uint8_t* dst = f.out_rgba8 + colour_index(f, x0, oy) * 3 + 4 * sx;
+    uint32_t w = 0;
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+      const int B = 4 * sx + b;
+      w |= (uint32_t)pb[(B / 3) * 4 + (B % 3)] << (8 * b);
+    }
+    if (4 * sx + 4 <= valid && (reinterpret_cast<uintptr_t>(dst) & 3u) == 0) *reinterpret_cast<uint32_t*>(dst) = w;
+    else
+      for (int b = 0; b < 4; b++)
+        if (4 * sx + b < valid) dst[b] = (uint8_t)(w >> (8 * b));
+    return;
+  }
   if (ox < f.p.tile_w && oy < f.rows_local) reinterpret_cast<uchar4*>(f.out_rgba8)[colour_index(f, ox, oy)] = patch[sy][sx];
 }
 

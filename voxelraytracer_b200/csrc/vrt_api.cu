@@ -40,6 +40,7 @@ struct vrt_ctx {
   unsigned long long* d_counters = nullptr;  // CNT_N
   unsigned long long* d_stats = nullptr;     // repack stats: [0] occupied voxels
   int64_t last_pixels = 0;
+  int last_bpp = 4;                // bytes per pixel of the last colour target (3 with VRT_FLAG_RGB8_OUT)
   cudaStream_t last_stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool timed = false;
@@ -300,7 +301,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   a.rows_local = (int)(npix / p->tile_w);
   finish_frame_args(a);
   CU(cudaEventRecord(ctx->ev0, s));
-  if ((p->flags & VRT_FLAG_PERSISTENT) && !debug && !(p->flags & VRT_FLAG_EXACT)) {
+  if ((p->flags & VRT_FLAG_PERSISTENT) && !debug && !(p->flags & (VRT_FLAG_EXACT | VRT_FLAG_RGB8_OUT))) {
     CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, (unsigned int*)(ctx->d_stats + 4), ctx->num_sms, s));
   } else {
     CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, remote_target(ctx, d_out), s));
@@ -309,6 +310,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   ctx->launches += 1;
   ctx->timed = true;
   ctx->last_pixels = npix;
+  ctx->last_bpp = (p->flags & VRT_FLAG_RGB8_OUT) ? 3 : 4;
   ctx->last_stream = s;
   return VRT_OK;
 }
@@ -335,7 +337,7 @@ int vrt_render_host(vrt_ctx* ctx, const vrt_params* p, uint8_t* host_rgba8, void
     }
   }
   if ((rc = render_impl(ctx, p, nullptr, (cudaStream_t)stream))) return rc;
-  CU(cudaMemcpyAsync(host_rgba8, ctx->d_fb, (size_t)ctx->last_pixels * 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CU(cudaMemcpyAsync(host_rgba8, ctx->d_fb, (size_t)ctx->last_pixels * ctx->last_bpp, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   CU(cudaStreamSynchronize((cudaStream_t)stream));
   return VRT_OK;
 }
@@ -343,18 +345,18 @@ int vrt_render_host(vrt_ctx* ctx, const vrt_params* p, uint8_t* host_rgba8, void
 int vrt_framebuffer_device(vrt_ctx* ctx, void** d_rgba8, size_t* bytes) {
   if (!ctx || !d_rgba8) return fail(ctx, VRT_E_INVALID, "vrt_framebuffer_device: NULL argument");
   *d_rgba8 = ctx->d_fb;
-  if (bytes) *bytes = (size_t)ctx->last_pixels * 4;
+  if (bytes) *bytes = (size_t)ctx->last_pixels * ctx->last_bpp;
   return ctx->d_fb ? VRT_OK : fail(ctx, VRT_E_NOT_READY, "vrt_framebuffer_device: nothing rendered yet");
 }
 
 int vrt_read_framebuffer(vrt_ctx* ctx, uint8_t* host, size_t bytes) {
   if (!ctx || !host) return fail(ctx, VRT_E_INVALID, "vrt_read_framebuffer: NULL argument");
   if (!ctx->d_fb || ctx->last_pixels == 0) return fail(ctx, VRT_E_NOT_READY, "vrt_read_framebuffer: nothing rendered yet");
-  if (bytes < (size_t)ctx->last_pixels * 4) return fail(ctx, VRT_E_INVALID, "vrt_read_framebuffer: buffer %zu < %zu bytes", bytes, (size_t)ctx->last_pixels * 4);
+  if (bytes < (size_t)ctx->last_pixels * ctx->last_bpp) return fail(ctx, VRT_E_INVALID, "vrt_read_framebuffer: buffer %zu < %zu bytes", bytes, (size_t)ctx->last_pixels * ctx->last_bpp);
   int rc = bind(ctx);
   if (rc) return rc;
   CU(cudaStreamSynchronize(ctx->last_stream));
-  CU(cudaMemcpy(host, ctx->d_fb, (size_t)ctx->last_pixels * 4, cudaMemcpyDeviceToHost));
+  CU(cudaMemcpy(host, ctx->d_fb, (size_t)ctx->last_pixels * ctx->last_bpp, cudaMemcpyDeviceToHost));
   return VRT_OK;
 }
 
