@@ -569,6 +569,11 @@ def run_ours(args):
         rays_all, steps_all, act_all, hits_all = float(rays), float(steps_ref), float(steps_act), float(hits)
 
     t_e2e = min(t_e2e_direct, t_e2e_staged)
+    l2_gbs = hbm_probe_gbs = None
+    if rank == 0:
+        # denominators measured on this box, outside every timed region: L2-resident and HBM-sized read sweeps
+        l2_gbs = ctx.probe_read_gbs(32 << 20, 400)
+        hbm_probe_gbs = ctx.probe_read_gbs(4 << 30, 4)
     if rank == 0:
         peaks = {}
         try:
@@ -609,6 +614,10 @@ def run_ours(args):
             "roofline_hbm": {"bound": "hbm", "achieved": bytes_per_launch / per_launch_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                              "frac": bytes_per_launch / per_launch_s / 1e9 / hbm_peak, "traffic": NCU_TRAFFIC.get(args.workload),
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"},
+            "roofline_l2": {"bound": "l2", "achieved": bytes_per_launch / per_launch_s / 1e9, "peak": l2_gbs, "unit": "GB/s",
+                            "frac": bytes_per_launch / per_launch_s / 1e9 / l2_gbs if l2_gbs else None,
+                            "peak_source": "vrt_probe_read_gbs: 32 MiB buffer read 400 times by one kernel on this GPU, just now",
+                            "hbm_probe_gbs": hbm_probe_gbs, "hbm_probe": "same kernel, 4 GiB buffer, 4 passes"},
             "e2e": {"value": rays_all / t_e2e / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(vrt.Params), "d2h_bytes_per_step": my_pix * 4,
                     "call": ("vrt_render_to into pinned host memory (the render kernel's 128-byte row stores cross PCIe; no device frame, no copy)"
                              if t_e2e_direct <= t_e2e_staged else "vrt_render_to + vrt_copy_to_host_async")

@@ -181,6 +181,10 @@ int vrt_host_free(vrt_ctx* ctx, void* p);
 int vrt_device_alloc(vrt_ctx* ctx, size_t bytes, void** out);
 int vrt_device_free(vrt_ctx* ctx, void* p);
 int vrt_synchronize(vrt_ctx* ctx, void* stream);
+/* Measurement helper (no counterpart in the reference): read bandwidth in GB/s of a `bytes`-sized device buffer read
+ * `passes` times by one kernel - 32 MiB stays in L2 (the denominator of the byte roofline), several GiB
+ * measure HBM. */
+int vrt_probe_read_gbs(vrt_ctx* ctx, size_t bytes, int passes, float* gbs);
 int vrt_copy_to_host(vrt_ctx* ctx, void* host, const void* d_src, size_t bytes, void* stream);   /* async on `stream`, then synchronised */
 int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes, void* stream); /* async on `stream`, then synchronised */
 /* Not synchronised: `host` should be pinned (vrt_host_alloc) and must not be read before vrt_synchronize(ctx, stream).

@@ -24,7 +24,7 @@ SCENE_TERRAIN, SCENE_GLASS_CUBE, SCENE_REFRACTION, SCENE_SYNTHETIC = 0, 1, 2, 3
 # every symbol include/vrt.h declares (tests check that the library exports all of them)
 EXPORTS = [
     "vrt_default_params", "vrt_abi_version", "vrt_create", "vrt_destroy", "vrt_last_error", "vrt_upload_grid",
-    "vrt_upload_grid_device", "vrt_upload_atlas", "vrt_render", "vrt_render_to", "vrt_render_host", "vrt_tile_pixels",
+    "vrt_upload_grid_device", "vrt_upload_atlas", "vrt_render", "vrt_render_to", "vrt_render_host", "vrt_tile_pixels", "vrt_probe_read_gbs",
     "vrt_framebuffer_device", "vrt_read_framebuffer", "vrt_read_debug_maps", "vrt_read_float_frame", "vrt_reset_counters",
     "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells", "vrt_set_option",
     "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_host_async", "vrt_copy_to_device", "vrt_temporal_blend", "vrt_temporal_filter",
@@ -104,6 +104,7 @@ def load_library():
         "vrt_render": (i32, [vp, PP, vp]),
         "vrt_render_to": (i32, [vp, PP, vp, vp]),
         "vrt_render_host": (i32, [vp, PP, vp, vp]),
+        "vrt_probe_read_gbs": (i32, [vp, C.c_size_t, i32, C.POINTER(C.c_float)]),
         "vrt_tile_pixels": (i64, [PP]),
         "vrt_framebuffer_device": (i32, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
         "vrt_read_framebuffer": (i32, [vp, vp, C.c_size_t]),
@@ -278,6 +279,12 @@ class Context:
 
     def render_to(self, p, d_ptr, stream=None):
         self._check(self.lib.vrt_render_to(self.h, C.byref(p), d_ptr, stream))
+
+    def probe_read_gbs(self, nbytes, passes):
+        """Read bandwidth (GB/s) of an nbytes buffer read `passes` times by one kernel: L2 for 32 MiB, HBM for GiBs."""
+        g = C.c_float()
+        self._check(self.lib.vrt_probe_read_gbs(self.h, nbytes, passes, C.byref(g)))
+        return float(g.value)
 
     def render_host(self, p, host_ptr, stream=None):
         self._check(self.lib.vrt_render_host(self.h, C.byref(p), host_ptr, stream))

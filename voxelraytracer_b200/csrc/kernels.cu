@@ -62,14 +62,19 @@ __device__ __forceinline__ void render_one(const FrameArgs& f, int lx, int ly, u
   }
 }
 
-// WX x WY warps per CTA (always 4 warps = kThreads).  Two arrangements are instantiated:
+// WX x WY warps per CTA.  Two arrangements are instantiated:
 //   2 x 2 -> 16 x 8 pixel patch, 64-byte rows: best 2D locality, the default for frames in this GPU's own memory
 //            (+5 % at C5, +2 % at C4 over 4 x 1, equal at C2);
 //   4 x 1 -> 32 x 4 pixel patch, full 128-byte rows: what a REMOTE frame behind NVLink wants (8-GPU fused gather:
 //            0.102 ms per step instead of 0.112 with 64-byte and 0.143 with 32-byte row pieces).
+#ifndef VRT_LOCAL_WX
+#define VRT_LOCAL_WX 2
+#define VRT_LOCAL_WY 2
+#endif
+// resident warps per SM stay at VRT_MIN_BLOCKS x 4 whatever the CTA size (at most 32 CTAs fit on an SM)
+constexpr int min_ctas(int warps) { return VRT_MIN_BLOCKS * 4 / warps > 32 ? 32 : (VRT_MIN_BLOCKS * 4 / warps > 0 ? VRT_MIN_BLOCKS * 4 / warps : 1); }
 template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY>
-__global__ void VRT_BOUNDS render_kernel(const __grid_constant__ FrameArgs f) {
-  static_assert(WX * WY * 32 == kThreads, "4 warps per CTA");
+__global__ void __launch_bounds__(WX * WY * 32, min_ctas(WX * WY)) render_kernel(const __grid_constant__ FrameArgs f) {
   constexpr int CW = kWarpW * WX, CH = kWarpH * WY;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int lx = blockIdx.x * CW + (warp % WX) * kWarpW + (lane & (kWarpW - 1));
@@ -148,18 +153,19 @@ static cudaError_t launch_variant(const FrameArgs& a, cudaStream_t s) {
   constexpr int CW = kWarpW * WX, CH = kWarpH * WY;
   dim3 grid((unsigned)((a.p.tile_w + CW - 1) / CW), (unsigned)((a.rows_local + CH - 1) / CH));
   if (grid.x == 0 || grid.y == 0) return cudaSuccess;
-  render_kernel<Tracer, FLAT, DEBUG, WX, WY><<<grid, kThreads, 0, s>>>(a);
+  render_kernel<Tracer, FLAT, DEBUG, WX, WY><<<grid, WX * WY * 32, 0, s>>>(a);
   return cudaGetLastError();
 }
 
 cudaError_t launch_render(const FrameArgs& a, bool exact, bool flat, bool debug, bool wide_rows, cudaStream_t s) {
+  constexpr int LX = VRT_LOCAL_WX, LY = VRT_LOCAL_WY;
   if (exact) {
     if (flat) return debug ? launch_variant<ExactTracer<true, true>, true, true, 2, 2>(a, s) : launch_variant<ExactTracer<true, false>, true, false, 2, 2>(a, s);
     return debug ? launch_variant<ExactTracer<false, true>, false, true, 2, 2>(a, s) : launch_variant<ExactTracer<false, false>, false, false, 2, 2>(a, s);
   }
   if (debug) return flat ? launch_variant<FastTracer<true, true>, true, true, 2, 2>(a, s) : launch_variant<FastTracer<false, true>, false, true, 2, 2>(a, s);
   if (wide_rows) return flat ? launch_variant<FastTracer<true, false>, true, false, 4, 1>(a, s) : launch_variant<FastTracer<false, false>, false, false, 4, 1>(a, s);
-  return flat ? launch_variant<FastTracer<true, false>, true, false, 2, 2>(a, s) : launch_variant<FastTracer<false, false>, false, false, 2, 2>(a, s);
+  return flat ? launch_variant<FastTracer<true, false>, true, false, LX, LY>(a, s) : launch_variant<FastTracer<false, false>, false, false, LX, LY>(a, s);
 }
 
 }  // namespace vrt

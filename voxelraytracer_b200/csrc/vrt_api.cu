@@ -465,6 +465,34 @@ int vrt_temporal_filter(vrt_ctx* ctx, const void* d_new, const void* d_old, void
   return VRT_OK;
 }
 
+int vrt_probe_read_gbs(vrt_ctx* ctx, size_t bytes, int passes, float* gbs) {
+  if (!ctx || !gbs || bytes < (1u << 20) || bytes > ((size_t)8 << 30) || passes < 1 || passes > 100000)
+    return fail(ctx, VRT_E_INVALID, "vrt_probe_read_gbs: bytes in [1 MiB, 8 GiB], passes in [1, 100000]");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  void* buf = nullptr;
+  if (cudaMalloc(&buf, bytes) != cudaSuccess) { cudaGetLastError(); return fail(ctx, VRT_E_CUDA, "vrt_probe_read_gbs: cannot allocate %zu bytes", bytes); }
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  cudaError_t e = cudaMemset(buf, 0, bytes);
+  if (e == cudaSuccess) e = cudaEventCreate(&e0);
+  if (e == cudaSuccess) e = cudaEventCreate(&e1);
+  unsigned int* sink = (unsigned int*)(ctx->d_stats + 6);
+  if (e == cudaSuccess) e = launch_read_probe(buf, bytes, 1, ctx->num_sms, sink, nullptr);     // warm-up: brings the buffer into L2 if it fits
+  if (e == cudaSuccess) e = cudaEventRecord(e0, nullptr);
+  if (e == cudaSuccess) e = launch_read_probe(buf, bytes, passes, ctx->num_sms, sink, nullptr);
+  if (e == cudaSuccess) e = cudaEventRecord(e1, nullptr);
+  if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+  float ms = 0.0f;
+  if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  cudaFree(buf);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(ctx, VRT_E_CUDA, "vrt_probe_read_gbs: %s", cudaGetErrorString(e)); }
+  ctx->launches += 2;
+  *gbs = ms > 0.0f ? (float)((double)(bytes / 16 * 16) * passes / (ms * 1e6)) : 0.0f;
+  return VRT_OK;
+}
+
 int vrt_host_alloc(vrt_ctx* ctx, size_t bytes, void** out) {
   if (!ctx || !out) return fail(ctx, VRT_E_INVALID, "vrt_host_alloc: NULL argument");
   int rc = bind(ctx);

@@ -24,6 +24,7 @@ cudaError_t launch_repack_octants(const uint8_t* d_grid, int n, int radius_cap, 
                                   uint16_t* d_cells, unsigned long long* d_stats, cudaStream_t stream, int* launches);
 
 // temporal.cu
+cudaError_t launch_read_probe(const void* d_buf, size_t bytes, int passes, int num_sms, unsigned int* sink, cudaStream_t stream);
 cudaError_t launch_temporal_blend(const uint8_t* d_new, const uint8_t* d_old, uint8_t* d_out, int64_t npix, float alpha, cudaStream_t stream);
 
 }  // namespace vrt
