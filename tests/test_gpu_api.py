@@ -155,3 +155,13 @@ def test_async_host_copy_and_radius_cap_option(ctx):
     finally:
         ctx.set_option(vrt.OPT_RADIUS_CAP, 0)
         ctx.upload_grid(grid, n)
+
+
+def test_read_bandwidth_probe(ctx):
+    """vrt_probe_read_gbs: the L2-resident sweep is faster than the HBM-sized one, both in a sane range for a B200."""
+    l2 = ctx.probe_read_gbs(32 << 20, 50)
+    hbm = ctx.probe_read_gbs(1 << 30, 2)
+    assert 1000.0 < hbm < 9000.0
+    assert hbm < l2 < 40000.0
+    with pytest.raises(vrt.VrtError):
+        ctx.probe_read_gbs(1024, 1)
