@@ -81,6 +81,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--octants", type=int, default=1, choices=[0, 1], help="VRT_OPT_OCTANT_FIELDS (tuning comparison; 1 = default)")
     ap.add_argument("--radius-cap", type=int, default=0, help="VRT_OPT_RADIUS_CAP (tuning comparison; 0 = default)")
+    ap.add_argument("--no-affinity", action="store_true", help="N > 1: do not restrict each rank to its GPU's local host cores")
     ap.add_argument("--e2e-depth", type=int, default=4, help="frames in flight in the overlapped e2e leg")
     ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
     return ap.parse_args()
@@ -227,6 +228,23 @@ def nvml_index(torch, local):
     return local
 
 
+def pin_to_gpu_cores(index):
+    """Restricts this process to the host cores NVML reports as local to GPU `index` (NUMA placement of the pinned frame
+    buffers follows the allocating thread).  Returns the number of cores, or None if it could not be done."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        words = (max(os.cpu_count() or 64, 64) + 63) // 64
+        mask = nv.nvmlDeviceGetCpuAffinity(nv.nvmlDeviceGetHandleByIndex(index), words)
+        cpus = {w * 64 + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1} & os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return None
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -240,6 +258,8 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    # N > 1: each rank's frames go to pinned host memory next to ITS GPU (8 ranks allocating on one socket halve the e2e leg)
+    host_cores = pin_to_gpu_cores(nvml_index(torch, local)) if world > 1 and not args.no_affinity else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     sc, poses, W, H, flags = WORKLOADS[args.workload]
@@ -601,7 +621,9 @@ def run_ours(args):
             "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD_DESC[args.workload], "poses": poses if len(poses) <= 8 else "%d orbit poses" % len(poses), "frame": [W, H], "traversal": args.mode, "sharding": shard,
                        "l2": "flushed: 256 MiB fill before every timed step window (the fill itself is outside the window)",
-                       "maxRayLength": MAX_LEN.get(args.workload, 100.0)},
+                       "maxRayLength": MAX_LEN.get(args.workload, 100.0),
+                       "host_affinity": None if world == 1 else ("rank 0 on the %d host cores local to its GPU (NVML), likewise every rank" % host_cores
+                                                                 if host_cores else "not set")},
             "frames_per_s": frames_total / t_step_total,
             "kernel_ms_per_launch": 1e3 * t_kernel_max / args.steps,
             "rays_per_frame": rays_all / frames_total, "ref_steps_per_frame": steps_all / frames_total,
