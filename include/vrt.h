@@ -193,7 +193,8 @@ int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes
 int vrt_copy_to_host_async(vrt_ctx* ctx, void* host, const void* d_src, size_t bytes, void* stream);
 
 /* ---- temporal accumulation pass (res/shaders/temporal.glsl:13-19; main.cpp:363-376,388-393) ----
- * acc = alpha * new + (1 - alpha) * acc on RGBA8 device buffers, n pixels. */
+ * acc = alpha * new + (1 - alpha) * acc on RGBA8 device buffers, n pixels.  Channels are blended independently, so a packed
+ * RGB8 frame (VRT_FLAG_RGB8_OUT) of w*h pixels is passed as npix = w*h*3/4 when w*h*3 is a multiple of 4. */
 int vrt_temporal_blend(vrt_ctx* ctx, const void* d_new_rgba8, void* d_acc_rgba8, int64_t npix, float alpha, void* stream);
 /* Same pass in the reference's three-target form: out = alpha * new + (1 - alpha) * old, with `new` = rayTraceFrameBuffer,
  * `old` = lastFrameBuffer, `out` = currentFrameBuffer (main.cpp:363-376); out may alias old. */

@@ -118,3 +118,16 @@ def test_fast_tracer_with_noise_uniforms():
         f = hostsim_render(p, grid, atlas, 1)
         assert int((f.hit != o.hit).sum()) <= max(3, int(1e-4 * 320 * 180)), sc       # primary hit map
         assert np.abs(f.rgba8.astype(float).mean(axis=0) - o.rgba8.astype(float).mean(axis=0)).max() < 2.0   # same image statistically
+
+
+def test_randomised_poses_terminate_and_exact_replay_stays_bit_exact():
+    """A slice of tools/fuzz_hostsim.py: random cameras inside / around / on the chunk, random caps and bounce limits.  Every
+    case runs in its own process under a timeout (a walk that never ends is a failure, not a hang of the suite)."""
+    import json, os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "fuzz_hostsim.py"), "--cases", "48", "--seed", "7", "--jobs", "4", "--timeout", "90"],
+                       capture_output=True, text=True, timeout=600)
+    line = json.loads(r.stdout.splitlines()[0])
+    assert line["hung_or_crashed"] == 0, r.stdout
+    assert line["exact_not_bit_exact"] == 0, r.stdout
+    assert line["mismatch_frac"] < 5e-4, r.stdout          # lattice-aligned cameras included (whole pixel lines on voxel edges)
