@@ -62,7 +62,10 @@ WORKLOAD_DESC = {
 }
 I_STEP = 16          # algorithmic thread-instructions per reference DDA step
 # dram__bytes_read.sum + dram__bytes_write.sum per render_kernel launch from the committed `ncu --set full` capture (profiles/)
-NCU_TRAFFIC = {"c2": 3.3e6, "c5": 3.4e9}   # profiles/r01_ncu_c2_final.txt, r01_ncu_c5.txt
+NCU_TRAFFIC = {"c2": 3.5e6, "c5": 3.4e9}   # dram read + write per launch: profiles/r01_ncu_c2_end.txt, r01_ncu_c5.txt
+# smsp__issue_active (share of issue slots really used, i.e. the fraction of the issue roofline without the credit for skipped
+# steps) and executed thread-instructions per launch from the same captures; static numbers from profiles/, not measured by this run
+NCU_ISSUE = {"c2": (0.843, "profiles/r01_ncu_c2_end.txt"), "c4": (0.844, "profiles/r01_ncu_c4.txt"), "c5": (0.777, "profiles/r01_ncu_c5.txt")}
 
 
 def parse():
@@ -632,7 +635,9 @@ def run_ours(args):
             "roofline": {"bound": "issue", "achieved": ach_issue / 1e12, "peak": p_issue / 1e12, "unit": "Tinstr/s", "frac": ach_issue / p_issue,
                          "traffic": NCU_TRAFFIC.get(args.workload), "traffic_unit": "DRAM bytes per launch (ncu --set full)",
                          "peak_source": "%d SM x 4 schedulers x 32 lanes x sampled SM clock %.0f MHz" % (sms, f_mhz),
-                         "algorithmic": "%d thread-instr per reference DDA step x reference steps (SURVEY.md 8(d))" % I_STEP},
+                         "algorithmic": "%d thread-instr per reference DDA step x reference steps (SURVEY.md 8(d)); empty-space skipping executes "
+                                        "fewer steps than the reference takes, hence frac > 1 is possible" % I_STEP,
+                         "issue_slots_busy_ncu": NCU_ISSUE.get(args.workload, (None, None))[0], "issue_slots_busy_source": NCU_ISSUE.get(args.workload, (None, None))[1]},
             "roofline_hbm": {"bound": "hbm", "achieved": bytes_per_launch / per_launch_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                              "frac": bytes_per_launch / per_launch_s / 1e9 / hbm_peak, "traffic": NCU_TRAFFIC.get(args.workload),
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"},
