@@ -163,11 +163,7 @@ VRT_HD void set_dir_const(DirConst& w, const V3& d, int P) {
   w.tdel = mk3(zx ? 0.0f : fabsf(w.inv.x), zy ? 0.0f : fabsf(w.inv.y), zz ? 0.0f : fabsf(w.inv.z));
   w.off = mk3(d.x >= 0.0f ? 1.0f : 0.0f, d.y >= 0.0f ? 1.0f : 0.0f, d.z >= 0.0f ? 1.0f : 0.0f);
   // 1 / max|d| == min |1/d| exactly (correctly rounded reciprocals are monotone); zero components are +inf and drop out
-#ifdef VRT_OLD_INVMAX
-  w.invmax = 1.0f / fmaxf(fabsf(d.x), fmaxf(fabsf(d.y), fabsf(d.z)));
-#else
   w.invmax = fminf(fabsf(w.inv.x), fminf(fabsf(w.inv.y), fabsf(w.inv.z)));
-#endif
   w.jbias = 1.015625f * w.invmax;
   w.dix = d.x > 0.0f ? 1 : -1;
   w.diy = d.y > 0.0f ? P : -P;

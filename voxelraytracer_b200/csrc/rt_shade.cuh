@@ -75,12 +75,7 @@ struct PixelCtx {
     MatProps m = material_of<false>(voxel);
     float fa = a - floorf(a), fb = b - floorf(b);
     float ts = (float)f.p.atlasTextureSize, as = (float)f.p.atlasSize;
-#ifdef VRT_OLD_TEX
-    const bool lean_tex = false;
-#else
-    const bool lean_tex = LEAN;
-#endif
-    if (lean_tex) {   // one per-frame ratio instead of two divisions; identical when both sizes are powers of two (16/32, 128/256)
+    if (LEAN) {   // one per-frame ratio instead of two divisions; identical when both sizes are powers of two (16/32, 128/256)
       *u = (fa + (float)m.tx) * f.tex_scale;
       *v = 1.0f - ((1.0f - fb) + (float)m.ty) * f.tex_scale;
     } else {

@@ -27,16 +27,6 @@
 
 namespace vrt {
 
-#ifndef VRT_IBIAS_SRC
-#define VRT_IBIAS_SRC cx.f.ibias
-#endif
-#ifndef VRT_PITCH_SRC
-#ifdef VRT_OLD_PITCH
-#define VRT_PITCH_SRC (n + 2)
-#else
-#define VRT_PITCH_SRC cx.f.pitch
-#endif
-#endif
 #ifndef VRT_JUMP_MIN
 #define VRT_JUMP_MIN 3
 #endif
@@ -194,7 +184,7 @@ struct FastTracer {
     float tlim = u2f(f2u(tcap) - 1u);                      // next float below tcap
     for (;;) {
       // a successful jump implies w.t < tn < tcap, so only the stepping path tests the cap itself
-      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tlim, P, VRT_IBIAS_SRC))) {
+      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tlim, P, cx.f.ibias))) {
         if (!(w.t < tcap)) return 0xFFFFFFFFu;
         // one step, or two for rad == 2, as a real (not if-converted) loop: predicated-off instructions of an unneeded
         // second step would still cost issue slots, and issue is the bound
@@ -213,13 +203,9 @@ struct FastTracer {
 
   static VRT_HD bool shadow(Ctx& cx, const Ray& r, const Hit&) {
     cx.count(CNT_SHADOW);
-    const int n = cx.f.p.size, P = VRT_PITCH_SRC;
+    const int n = cx.f.p.size, P = cx.f.pitch;
     const DirConst& k = cx.f.sun;                          // shadow rays all point at the sun (voxel.glsl:191-201)
-#ifdef VRT_OLD_SUNCELLS
-    const uint16_t* cells = cx.f.cells + (size_t)k.oct * cx.f.oct_stride;
-#else
-    const uint16_t* cells = cx.f.sun_cells;
-#endif
+    const uint16_t* cells = cx.f.sun_cells;                // the sun octant's radius field
     const float tcap = cx.f.p.maxRayLength - r.len;
     Walk w;
     if (!begin(w, k, r, cx.f.fsize, n, P)) return false;
@@ -235,7 +221,7 @@ struct FastTracer {
   static VRT_HD Hit march(Ctx& cx, Ray& r) {
     Hit h;
     h.found = false;
-    const int n = cx.f.p.size, P = VRT_PITCH_SRC;
+    const int n = cx.f.p.size, P = cx.f.pitch;
     DirConst k;
     set_dir_const(k, r.dir, P);
     const uint16_t* cells = cx.f.cells + (size_t)k.oct * cx.f.oct_stride;
