@@ -154,11 +154,12 @@ int64_t vrt_kernel_launches(const vrt_ctx* ctx);
 /* ---- repacked grid inspection (tests) ----
  * The upload repacks the chunk into traversal cells: arrays of (size+2)^3 uint16 with a one-cell border of 0,
  * cell = (emptyRadius << 8) | voxelByte, index (x+1) + (y+1)*pitch + (z+1)*pitch^2, emptyRadius capped at radius_cap
- * and 0 for occupied and border cells.
+ * and 0 for occupied and border cells.  Space outside the chunk counts as empty (the walk bounds its jumps by the ray's
+ * exit time); only the value 2 is withheld (1 instead) from cells whose forward neighbour is outside the chunk.
  *   octants == 8 (default): eight arrays back to back, array o = (dx < 0) | (dy < 0) << 1 | (dz < 0) << 2 serves rays of
- *     that direction octant; emptyRadius = edge of the largest empty in-chunk box that starts at the cell and extends
- *     FORWARD along the octant's signs (forward Chebyshev distance to the nearest occupied or border cell).
- *   octants == 1: one array; emptyRadius = Chebyshev distance to the nearest occupied or border cell in any direction. */
+ *     that direction octant; emptyRadius = edge of the largest box without an occupied voxel that starts at the cell and
+ *     extends FORWARD along the octant's signs (forward Chebyshev distance to the nearest occupied cell).
+ *   octants == 1: one array; emptyRadius = Chebyshev distance to the nearest occupied cell in any direction. */
 typedef struct vrt_grid_info {
   int32_t size, pitch, radius_cap, octants;
   int64_t cells_total, voxels_occupied;

@@ -12,6 +12,7 @@
 #include "../../voxelraytracer_b200/csrc/rt_trace_fast.cuh"
 
 #include <atomic>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -21,21 +22,21 @@ using namespace vrt;
 extern "C" {
 
 // CPU statement of the repack (voxelraytracer_b200/csrc/repack.cu): padded (n+2)^3 uint16 cells,
-// low byte = voxel, high byte = Chebyshev distance to the nearest occupied-or-border cell (cap 255).
+// low byte = voxel, high byte = Chebyshev distance to the nearest occupied cell (cap 255); outside the chunk is empty.
 int hostsim_build_cells(const uint8_t* grid, int n, uint16_t* cells) {
   const int P = n + 2;
   std::vector<uint8_t> a((size_t)n * n * n), b((size_t)n * n * n);
   auto at = [n](int x, int y, int z) { return (size_t)x + (size_t)y * n + (size_t)z * n * n; };
   auto cap = [](int v) { return (uint8_t)(v > 255 ? 255 : v); };
-  // pass x: distance along the row to the nearest occupied voxel or to the border cell (-1 or n)
+  // pass x: distance along the row to the nearest occupied voxel (nothing beyond the ends of the row)
   for (int z = 0; z < n; z++)
     for (int y = 0; y < n; y++) {
-      int d = 0;  // distance to the last obstacle seen; the border cell at x = -1 is an obstacle
+      int d = 1 << 20;  // distance to the last obstacle seen: none yet
       for (int x = 0; x < n; x++) { d = grid[at(x, y, z)] ? 0 : d + 1; a[at(x, y, z)] = cap(d); }
-      d = 0;
+      d = 1 << 20;
       for (int x = n - 1; x >= 0; x--) { d = grid[at(x, y, z)] ? 0 : d + 1; if (d < a[at(x, y, z)]) a[at(x, y, z)] = cap(d); }
     }
-  // pass y, z: D(y) = min_k max(|k|, D'(y+k)), border at distance y+1 / n-y
+  // pass y, z: D(y) = min_k max(|k|, D'(y+k)) over the cells of the chunk
   for (int pass = 0; pass < 2; pass++) {
     const std::vector<uint8_t>& src = pass == 0 ? a : b;
     std::vector<uint8_t>& dst = pass == 0 ? b : a;
@@ -44,8 +45,6 @@ int hostsim_build_cells(const uint8_t* grid, int n, uint16_t* cells) {
         for (int x = 0; x < n; x++) {
           int c = pass == 0 ? y : z;
           int best = src[at(x, y, z)];
-          int edge = c + 1 < n - c ? c + 1 : n - c;
-          if (edge < best) best = edge;
           for (int k = 1; k < best; k++) {
             int lo = c - k, hi = c + k;
             if (lo >= 0) { int v = pass == 0 ? src[at(x, lo, z)] : src[at(x, y, lo)]; int m = v > k ? v : k; if (m < best) best = m; }
@@ -60,14 +59,17 @@ int hostsim_build_cells(const uint8_t* grid, int n, uint16_t* cells) {
       for (int x = 0; x < n; x++) {
         uint8_t v = grid[at(x, y, z)];
         uint8_t r = v ? 0 : a[at(x, y, z)];
+        // radius 2 = two unchecked steps: not next to the one-cell border (see pack_cells in repack.cu)
+        if (r == 2 && (x == 0 || y == 0 || z == 0 || x == n - 1 || y == n - 1 || z == n - 1)) r = 1;
         cells[(size_t)(x + 1) + (size_t)(y + 1) * P + (size_t)(z + 1) * P * P] = (uint16_t)((r << 8) | v);
       }
   return 0;
 }
 
 // Octant fields: 8 arrays like the one above, array o for rays with direction signs s = (o&1 ? -1 : +1, o&2 ? -1 : +1,
-// o&4 ? -1 : +1).  High byte = largest k such that the forward box {c + s*d : d in [0,k)^3} is empty and inside the
-// chunk, capped at `cap` (0 for occupied cells) == forward Chebyshev distance to the nearest occupied-or-border cell.
+// o&4 ? -1 : +1).  High byte = largest k such that the forward box {c + s*d : d in [0,k)^3} holds no occupied voxel
+// (cells outside the chunk are empty), capped at `cap` (0 for occupied cells) == forward Chebyshev distance to the
+// nearest occupied cell.
 // Computed here with the maximal-cube recurrence D(c) = 1 + min over the 7 forward neighbours, an algorithm that
 // shares nothing with the separable one-sided scans of repack.cu.
 int hostsim_build_cells_oct(const uint8_t* grid, int n, int cap, uint16_t* cells) {
@@ -79,7 +81,7 @@ int hostsim_build_cells_oct(const uint8_t* grid, int n, int cap, uint16_t* cells
   for (int o = 0; o < 8; o++) {
     const int sx = o & 1 ? -1 : 1, sy = o & 2 ? -1 : 1, sz = o & 4 ? -1 : 1;
     auto get = [&](int x, int y, int z) -> int {
-      if (x < 0 || y < 0 || z < 0 || x >= n || y >= n || z >= n) return 0;  // border cells are obstacles
+      if (x < 0 || y < 0 || z < 0 || x >= n || y >= n || z >= n) return 255;  // outside the chunk is empty
       return D[at(x, y, z)];
     };
     for (int kz = 0; kz < n; kz++)
@@ -104,7 +106,9 @@ int hostsim_build_cells_oct(const uint8_t* grid, int n, int cap, uint16_t* cells
       for (int y = 0; y < n; y++)
         for (int x = 0; x < n; x++) {
           uint8_t v = grid[at(x, y, z)];
-          out[(size_t)(x + 1) + (size_t)(y + 1) * P + (size_t)(z + 1) * P * P] = (uint16_t)(((v ? 0 : D[at(x, y, z)]) << 8) | v);
+          int r = v ? 0 : D[at(x, y, z)];
+          if (r == 2 && (x == (sx > 0 ? n - 1 : 0) || y == (sy > 0 ? n - 1 : 0) || z == (sz > 0 ? n - 1 : 0))) r = 1;
+          out[(size_t)(x + 1) + (size_t)(y + 1) * P + (size_t)(z + 1) * P * P] = (uint16_t)((r << 8) | v);
         }
   }
   return 0;
@@ -175,5 +179,11 @@ int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cel
   if (counters) std::memcpy(counters, cnt, sizeof(cnt));
   return 0;
 }
+
+#ifdef VRT_HOST_HIST
+void hostsim_radius_hist(unsigned long long* out, int reset) {
+  for (int i = 0; i < 256; i++) { out[i] = vrt::g_radius_hist[i]; if (reset) vrt::g_radius_hist[i] = 0; }
+}
+#endif
 
 }  // extern "C"

@@ -1,8 +1,10 @@
 // repack.cu -- K2: raw R8 chunk (what glTexImage3D received, src/main.cpp:315-318) -> traversal cells.
 //
 // Output layout (consumed by rt_trace_fast.cuh): (n+2)^3 uint16, one-cell border of 0x0000,
-//   cell = (emptyRadius << 8) | voxelByte, emptyRadius = Chebyshev distance to the nearest occupied voxel
-//   or border cell, capped; 0 for occupied cells.
+//   cell = (emptyRadius << 8) | voxelByte, emptyRadius = Chebyshev distance to the nearest occupied voxel, capped;
+//   0 for occupied cells.  Space outside the chunk counts as EMPTY: the field looks through the boundary and the walk
+//   bounds its jumps by the ray's exit time instead (rt_trace_fast.cuh), so rays that leave through open sky need one
+//   jump, not a geometric series of ever shorter ones towards the border.
 // The L-infinity distance transform is separable: D = min over z' of max(|z-z'|, min over y' of
 // max(|y-y'|, dx(x, y', z'))).  Each pass is one thread per voxel scanning outward along one axis until the
 // ring radius reaches the best value found so far, so the work per voxel is O(result), and every pass is
@@ -29,17 +31,17 @@ __global__ void __launch_bounds__(256) distance_pass(const uint8_t* __restrict__
     } else {
       best = __ldg(src + i);
     }
-    best = imin(best, imin(c + 1, n - c));  // the border cells at -1 and n are obstacles
     for (int k = 1; k < best; k++) {
-      // ring k: both neighbours at distance k are inside the grid because k < best <= distance to the border
-      int lo, hi;
+      // ring k; a neighbour beyond the chunk is empty space (value cap) and cannot lower the result
+      int lo = cap, hi = cap;
       if (AXIS == 0) {
-        lo = __ldg(grid + i - (size_t)k) ? 0 : cap;
-        hi = __ldg(grid + i + (size_t)k) ? 0 : cap;
+        if (c - k >= 0) lo = __ldg(grid + i - (size_t)k) ? 0 : cap;
+        if (c + k < n) hi = __ldg(grid + i + (size_t)k) ? 0 : cap;
       } else {
-        lo = __ldg(src + i - (size_t)k * stride);
-        hi = __ldg(src + i + (size_t)k * stride);
+        if (c - k >= 0) lo = __ldg(src + i - (size_t)k * stride);
+        if (c + k < n) hi = __ldg(src + i + (size_t)k * stride);
       }
+      if (c - k < 0 && c + k >= n) break;
       best = imin(best, imax(k, imin(lo, hi)));
     }
     dst[i] = (uint8_t)best;
@@ -47,9 +49,9 @@ __global__ void __launch_bounds__(256) distance_pass(const uint8_t* __restrict__
 }
 
 // One-sided variant for the octant fields: forward distance along +axis (DIR = +1) or -axis (DIR = -1) only.
-//   D(c) = min over k >= 0 of max(k, src(c + k * DIR))   with the border cell (at -1 or n) as an obstacle,
-// so after the three passes the value is the forward Chebyshev distance to the nearest occupied-or-border cell in
-// the octant (sx, sy, sz), i.e. the edge of the largest empty box that starts at the cell and extends forward.
+//   D(c) = min over k >= 0 of max(k, src(c + k * DIR))   with everything beyond the chunk empty (value cap),
+// so after the three passes the value is the forward Chebyshev distance to the nearest occupied cell in the octant
+// (sx, sy, sz), i.e. the edge of the largest empty box that starts at the cell and extends forward (possibly out of the chunk).
 template <int AXIS, int DIR>
 __global__ void __launch_bounds__(256) forward_pass(const uint8_t* __restrict__ grid, const uint8_t* __restrict__ src,
                                                      uint8_t* __restrict__ dst, int n, int log2n, int cap) {
@@ -59,8 +61,8 @@ __global__ void __launch_bounds__(256) forward_pass(const uint8_t* __restrict__ 
     const int c = AXIS == 0 ? x : (AXIS == 1 ? y : z);
     const long long stride = (AXIS == 0 ? 1LL : (AXIS == 1 ? (long long)n : (long long)n * n)) * DIR;
     int best = AXIS == 0 ? (__ldg(grid + i) ? 0 : cap) : (int)__ldg(src + i);
-    best = imin(best, DIR > 0 ? n - c : c + 1);      // the border cell ahead is an obstacle
-    for (int k = 1; k < best; k++) {                  // k < best <= distance to the border: the neighbour is inside the grid
+    const int ahead = DIR > 0 ? n - c : c + 1;        // cells of the chunk from here on, this one included
+    for (int k = 1; k < best && k < ahead; k++) {     // beyond the chunk: empty space, no constraint
       const size_t j = (size_t)((long long)i + (long long)k * stride);
       const int v = AXIS == 0 ? (__ldg(grid + j) ? 0 : cap) : (int)__ldg(src + j);
       best = imin(best, imax(k, v));
@@ -76,8 +78,11 @@ static void launch_forward(int dir, unsigned blocks, const uint8_t* grid, const 
   else forward_pass<AXIS, -1><<<blocks, 256, 0, s>>>(grid, src, dst, n, log2n, cap);
 }
 
+// `fwd`: octant bits (bit a set = the field looks towards -a) or -1 for the isotropic field.  One exception to "outside is
+// empty": radius 2 means "two steps without looking at the cell in between" (rt_trace_fast.cuh), which must not walk
+// through the one-cell border, so a cell whose forward neighbour lies outside the chunk keeps radius 1 instead of 2.
 __global__ void __launch_bounds__(256) pack_cells(const uint8_t* __restrict__ grid, const uint8_t* __restrict__ radius,
-                                                   uint16_t* __restrict__ cells, int n, int log2n, unsigned long long* stats) {
+                                                   uint16_t* __restrict__ cells, int n, int log2n, int fwd, unsigned long long* stats) {
   const int P = n + 2;
   const size_t total = (size_t)P * P * P;
   unsigned occupied = 0;
@@ -87,7 +92,12 @@ __global__ void __launch_bounds__(256) pack_cells(const uint8_t* __restrict__ gr
     if ((unsigned)x < (unsigned)n && (unsigned)y < (unsigned)n && (unsigned)z < (unsigned)n) {
       const size_t g = (size_t)x + ((size_t)y << log2n) + ((size_t)z << (2 * log2n));
       const unsigned b = __ldg(grid + g);
-      const unsigned r = b ? 0u : (unsigned)__ldg(radius + g);
+      unsigned r = b ? 0u : (unsigned)__ldg(radius + g);
+      if (r == 2u) {
+        const bool edge = fwd < 0 ? (x == 0 || y == 0 || z == 0 || x == n - 1 || y == n - 1 || z == n - 1)
+                                  : (x == ((fwd & 1) ? 0 : n - 1) || y == ((fwd & 2) ? 0 : n - 1) || z == ((fwd & 4) ? 0 : n - 1));
+        if (edge) r = 1u;
+      }
       v = (uint16_t)((r << 8) | b);
       occupied += b ? 1u : 0u;
     }
@@ -115,7 +125,7 @@ cudaError_t launch_repack(const uint8_t* d_grid, int n, int radius_cap, uint8_t*
   const size_t ptotal = (size_t)(n + 2) * (n + 2) * (n + 2);
   size_t pwant = (ptotal + 255) / 256;
   unsigned pblocks = (unsigned)(pwant > 148u * 64u ? 148u * 64u : pwant);
-  pack_cells<<<pblocks, 256, 0, stream>>>(d_grid, tmp_a, d_cells, n, log2n, d_stats);
+  pack_cells<<<pblocks, 256, 0, stream>>>(d_grid, tmp_a, d_cells, n, log2n, -1, d_stats);
   if (launches) *launches = 4;
   return cudaGetLastError();
 }
@@ -140,7 +150,7 @@ cudaError_t launch_repack_octants(const uint8_t* d_grid, int n, int radius_cap, 
       for (int oz = 0; oz < 2; oz++) {
         launch_forward<2>(oz ? -1 : 1, blocks, d_grid, tmp_b, tmp_c, n, log2n, cap, stream); count++;
         const int o = ox | (oy << 1) | (oz << 2);
-        pack_cells<<<pblocks, 256, 0, stream>>>(d_grid, tmp_c, d_cells + (size_t)o * ptotal, n, log2n, o == 0 ? d_stats : nullptr); count++;
+        pack_cells<<<pblocks, 256, 0, stream>>>(d_grid, tmp_c, d_cells + (size_t)o * ptotal, n, log2n, o, o == 0 ? d_stats : nullptr); count++;
       }
     }
   }

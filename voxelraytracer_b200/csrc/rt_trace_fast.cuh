@@ -4,11 +4,14 @@
 // Data (built on the device by repack.cu at vrt_upload_grid):
 //   cells[(x+1) + (y+1)*P + (z+1)*P*P], P = n+2, one uint16 per voxel plus a one-voxel border:
 //     low byte  = the voxel byte (material), 0 for air
-//     high byte = empty radius r: Chebyshev distance to the nearest occupied voxel OR border cell,
+//     high byte = empty radius r: (forward, per direction octant) Chebyshev distance to the nearest occupied voxel,
 //                 capped at 255; r = 0 iff the cell is occupied or is a border cell.
-//   border cells are 0x0000 ("radius 0, byte 0") and terminate the walk: no per-step bounds test exists.
-//   An empty cell with radius r promises that every cell within Chebyshev distance r-1 is empty and
-//   inside the chunk.
+//   Space outside the chunk counts as empty: an empty cell with radius r promises that every cell of the chunk within
+//   (forward) Chebyshev distance r-1 is empty.  The box may reach past the chunk, so jumps are bounded by the time at
+//   which the ray leaves the chunk (texit in walk_air); a ray that exits through open sky needs one jump instead of a
+//   series of ever shorter ones towards the border.  Radius 2 ("two steps without a look in between") is the one value
+//   never given to a cell whose forward neighbour is outside, so plain steps cannot walk through the border.
+//   border cells are 0x0000 ("radius 0, byte 0") and terminate a walk that steps into them: no per-step bounds test exists.
 //
 // Walk (the cells visited are the ones the shader's DDA visits; what is skipped is the work):
 //   r >= kJumpMin : jump along the ray by (r-1) cells of dominant-axis travel, re-derive the cell and
@@ -29,6 +32,14 @@ namespace vrt {
 
 #ifndef VRT_JUMP_MIN
 #define VRT_JUMP_MIN 3
+#endif
+
+#if defined(VRT_HOST_HIST) && !defined(__CUDA_ARCH__)
+// tools/radius_hist.py: how many loop iterations start from a cell of radius r (host build only)
+static unsigned long long g_radius_hist[256];
+#define VRT_HIST(r) __atomic_fetch_add(&g_radius_hist[(r) & 255u], 1ull, __ATOMIC_RELAXED)
+#else
+#define VRT_HIST(r) ((void)0)
 #endif
 
 VRT_HD uint32_t load_cell(const uint16_t* cells, uint32_t idx) {
@@ -90,11 +101,14 @@ struct FastTracer {
   // hit (voxel.glsl:317-353) - are taken and tested one by one.  False only if that leaves no progress.
   // After such a shortened jump `tlim` is set below every walk time, so the rest of the walk is plain steps (a second
   // shortened jump could land on the same point again and, with plane times rounded behind it, never terminate).
-  static VRT_HD bool jump(Walk& w, const DirConst& k, uint32_t r, float& tlim, int P, uint32_t ibias) {
+  static VRT_HD bool jump(Walk& w, const DirConst& k, uint32_t r, float& tlim, bool exits, int P, uint32_t ibias) {
     // (float)r without a conversion instruction: 2^23 + r has r in its low mantissa bits
     const float rf = u2f(0x4B000000u | r) - 8388608.0f;
     float tn = fmaf(rf, k.invmax, w.t - k.jbias);
-    if (!(tn < tlim)) { tn = tlim; tlim = -1.0f; }
+    if (!(tn < tlim)) {
+      if (exits) { w.t = finf(); return false; }           // the empty box reaches past the chunk: the ray leaves it unobstructed
+      tn = tlim; tlim = -1.0f;
+    }
     if (!(tn > w.t)) return false;
     const float qx = fmaf(tn, k.d.x, w.o.x), qy = fmaf(tn, k.d.y, w.o.y), qz = fmaf(tn, k.d.z, w.o.z);
 #if defined(__CUDA_ARCH__)
@@ -182,9 +196,17 @@ struct FastTracer {
   static VRT_HD uint32_t walk_air(Ctx& cx, Walk& w, const DirConst& k, const uint16_t* cells, uint32_t rad, float tcap, int P) {
     if (!(tcap > 0.0f)) return 0xFFFFFFFFu;                // already at the length cap (w.t >= 0 always)
     float tlim = u2f(f2u(tcap) - 1u);                      // next float below tcap
+    // The radius field looks through the chunk boundary (outside counts as empty), so a jump may aim past it: the time
+    // at which the ray leaves the chunk bounds the jump instead.  Whichever of the two limits comes first decides what
+    // passing it means: past the exit = the ray is gone; past the cap = land just before it and step (see jump).
+    const float fs = cx.f.fsize;
+    const float texit = fminf((k.off.x * fs - w.o.x) * k.inv.x, fminf((k.off.y * fs - w.o.y) * k.inv.y, (k.off.z * fs - w.o.z) * k.inv.z));
+    const bool exits = texit <= tlim;
+    if (exits) tlim = texit;
     for (;;) {
+      VRT_HIST(rad);
       // a successful jump implies w.t < tn < tcap, so only the stepping path tests the cap itself
-      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tlim, P, cx.f.ibias))) {
+      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tlim, exits, P, cx.f.ibias))) {
         if (!(w.t < tcap)) return 0xFFFFFFFFu;
         // one step, or two for rad == 2, as a real (not if-converted) loop: predicated-off instructions of an unneeded
         // second step would still cost issue slots, and issue is the bound
