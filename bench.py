@@ -62,10 +62,10 @@ WORKLOAD_DESC = {
 }
 I_STEP = 16          # algorithmic thread-instructions per reference DDA step
 # dram__bytes_read.sum + dram__bytes_write.sum per render_kernel launch from the committed `ncu --set full` capture (profiles/)
-NCU_TRAFFIC = {"c2": 3.5e6, "c5": 3.4e9}   # dram read + write per launch: profiles/r01_ncu_c2_end.txt, r01_ncu_c5.txt
+NCU_TRAFFIC = {"c2": 2.9e6, "c5": 3.4e9}   # dram read + write per launch: profiles/r01_ncu_c2_end.txt, r01_ncu_c5.txt
 # smsp__issue_active (share of issue slots really used, i.e. the fraction of the issue roofline without the credit for skipped
 # steps) and executed thread-instructions per launch from the same captures; static numbers from profiles/, not measured by this run
-NCU_ISSUE = {"c2": (0.843, "profiles/r01_ncu_c2_end.txt"), "c4": (0.844, "profiles/r01_ncu_c4.txt"), "c5": (0.777, "profiles/r01_ncu_c5.txt")}
+NCU_ISSUE = {"c2": (0.850, "profiles/r01_ncu_c2_end.txt"), "c4": (0.844, "profiles/r01_ncu_c4.txt"), "c5": (0.777, "profiles/r01_ncu_c5.txt")}
 
 
 def parse():
