@@ -99,6 +99,24 @@ def test_temporal_blend_matches_formula(ctx):
     assert np.array_equal(got if alpha == 1.0 else a, a)
 
 
+def test_own_framebuffer_is_not_confused_with_caller_targets(ctx):
+    """vrt_framebuffer_device / vrt_read_framebuffer describe the ctx-owned frame (FrameBuffer::GetTexture, FrameBuffer.cpp:27-30)
+    even after a larger frame went to caller memory through vrt_render_to."""
+    grid, n, atlas, ts = scene("terrain32")
+    ctx.upload_grid(grid, n); ctx.upload_atlas(atlas, ts)
+    small = make_params(64, 48, "terrain32", "terrain32_above")
+    ctx.render(small)
+    want = ctx.read_framebuffer(small)
+    big = make_params(640, 400, "terrain32", "terrain32_above")
+    d = ctx.device_alloc(640 * 400 * 4)
+    ctx.render_to(big, d)
+    ctx.synchronize()
+    _, nbytes = ctx.framebuffer_device()
+    assert nbytes == 64 * 48 * 4
+    assert np.array_equal(ctx.read_framebuffer(small), want)
+    ctx.device_free(d)
+
+
 def test_two_contexts_are_independent():
     c1, c2 = vrt.Context(0), vrt.Context(0)
     g1, n1, a1, t1 = scene("glass_cube32")

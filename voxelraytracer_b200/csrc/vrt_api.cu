@@ -39,8 +39,9 @@ struct vrt_ctx {
   uint8_t* d_bounces = nullptr; size_t bounces_bytes = 0;
   unsigned long long* d_counters = nullptr;  // CNT_N
   unsigned long long* d_stats = nullptr;     // repack stats: [0] occupied voxels
-  int64_t last_pixels = 0;
-  int last_bpp = 4;                // bytes per pixel of the last colour target (3 with VRT_FLAG_RGB8_OUT)
+  int64_t last_pixels = 0;         // pixels of the last render (whatever its colour target): bounds the debug-map reads
+  int64_t fb_pixels = 0;           // pixels of the last render INTO d_fb (vrt_render / pageable vrt_render_host)
+  int fb_bpp = 4;                  // its bytes per pixel (3 with VRT_FLAG_RGB8_OUT)
   cudaStream_t last_stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool timed = false;
@@ -287,6 +288,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
     if ((rc = ensure(ctx, &ctx->d_fb, &ctx->fb_bytes, (size_t)npix * 4))) return rc;
     d_out = ctx->d_fb;
   }
+  const bool own_fb = d_out == ctx->d_fb;
   a.out_rgba8 = d_out;
   if (p->flags & VRT_FLAG_FLOAT_OUT) {
     if ((rc = ensure(ctx, &ctx->d_f32, &ctx->f32_bytes, (size_t)npix * 16))) return rc;
@@ -310,7 +312,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   ctx->launches += 1;
   ctx->timed = true;
   ctx->last_pixels = npix;
-  ctx->last_bpp = (p->flags & VRT_FLAG_RGB8_OUT) ? 3 : 4;
+  if (own_fb) { ctx->fb_pixels = npix; ctx->fb_bpp = (p->flags & VRT_FLAG_RGB8_OUT) ? 3 : 4; }
   ctx->last_stream = s;
   return VRT_OK;
 }
@@ -337,7 +339,7 @@ int vrt_render_host(vrt_ctx* ctx, const vrt_params* p, uint8_t* host_rgba8, void
     }
   }
   if ((rc = render_impl(ctx, p, nullptr, (cudaStream_t)stream))) return rc;
-  CU(cudaMemcpyAsync(host_rgba8, ctx->d_fb, (size_t)ctx->last_pixels * ctx->last_bpp, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CU(cudaMemcpyAsync(host_rgba8, ctx->d_fb, (size_t)ctx->fb_pixels * ctx->fb_bpp, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   CU(cudaStreamSynchronize((cudaStream_t)stream));
   return VRT_OK;
 }
@@ -345,18 +347,18 @@ int vrt_render_host(vrt_ctx* ctx, const vrt_params* p, uint8_t* host_rgba8, void
 int vrt_framebuffer_device(vrt_ctx* ctx, void** d_rgba8, size_t* bytes) {
   if (!ctx || !d_rgba8) return fail(ctx, VRT_E_INVALID, "vrt_framebuffer_device: NULL argument");
   *d_rgba8 = ctx->d_fb;
-  if (bytes) *bytes = (size_t)ctx->last_pixels * ctx->last_bpp;
+  if (bytes) *bytes = (size_t)ctx->fb_pixels * ctx->fb_bpp;
   return ctx->d_fb ? VRT_OK : fail(ctx, VRT_E_NOT_READY, "vrt_framebuffer_device: nothing rendered yet");
 }
 
 int vrt_read_framebuffer(vrt_ctx* ctx, uint8_t* host, size_t bytes) {
   if (!ctx || !host) return fail(ctx, VRT_E_INVALID, "vrt_read_framebuffer: NULL argument");
-  if (!ctx->d_fb || ctx->last_pixels == 0) return fail(ctx, VRT_E_NOT_READY, "vrt_read_framebuffer: nothing rendered yet");
-  if (bytes < (size_t)ctx->last_pixels * ctx->last_bpp) return fail(ctx, VRT_E_INVALID, "vrt_read_framebuffer: buffer %zu < %zu bytes", bytes, (size_t)ctx->last_pixels * ctx->last_bpp);
+  if (!ctx->d_fb || ctx->fb_pixels == 0) return fail(ctx, VRT_E_NOT_READY, "vrt_read_framebuffer: nothing rendered yet");
+  if (bytes < (size_t)ctx->fb_pixels * ctx->fb_bpp) return fail(ctx, VRT_E_INVALID, "vrt_read_framebuffer: buffer %zu < %zu bytes", bytes, (size_t)ctx->fb_pixels * ctx->fb_bpp);
   int rc = bind(ctx);
   if (rc) return rc;
   CU(cudaStreamSynchronize(ctx->last_stream));
-  CU(cudaMemcpy(host, ctx->d_fb, (size_t)ctx->last_pixels * ctx->last_bpp, cudaMemcpyDeviceToHost));
+  CU(cudaMemcpy(host, ctx->d_fb, (size_t)ctx->fb_pixels * ctx->fb_bpp, cudaMemcpyDeviceToHost));
   return VRT_OK;
 }
 
