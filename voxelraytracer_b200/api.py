@@ -74,7 +74,8 @@ class GridInfo(C.Structure):
 
 
 def lib_path():
-    return os.path.join(_HERE, "libvrt.so")
+    """In-tree libvrt.so; VRT_LIBRARY names another BUILD of it (tools/ab_time.py times kernel variants side by side)."""
+    return os.environ.get("VRT_LIBRARY") or os.path.join(_HERE, "libvrt.so")
 
 
 _lib = None

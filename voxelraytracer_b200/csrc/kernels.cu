@@ -77,17 +77,22 @@ template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY>
 __global__ void __launch_bounds__(WX * WY * 32, min_ctas(WX * WY)) render_kernel(const __grid_constant__ FrameArgs f) {
   constexpr int CW = kWarpW * WX, CH = kWarpH * WY;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef VRT_REV_Y
+  const int by = gridDim.y - 1 - blockIdx.y;
+#else
+  const int by = blockIdx.y;
+#endif
   const int lx = blockIdx.x * CW + (warp % WX) * kWarpW + (lane & (kWarpW - 1));
-  const int ly = blockIdx.y * CH + (warp / WX) * kWarpH + (lane / kWarpW);
+  const int ly = by * CH + (warp / WX) * kWarpH + (lane / kWarpW);
   // Rays are traced in 8x4 patches per warp (coherence), pixels are stored in rows: the CTA's patch goes through shared
   // memory and each thread stores the pixel at (tid % CW, tid / CW), so that a warp writes whole row segments.
   __shared__ uchar4 patch[CH][CW];
   uchar4 q = make_uchar4(0, 0, 0, 255);
   render_one<Tracer, FLAT, DEBUG, true>(f, lx, ly, &q);
-  patch[ly - blockIdx.y * CH][lx - blockIdx.x * CW] = q;
+  patch[ly - by * CH][lx - blockIdx.x * CW] = q;
   __syncthreads();
   const int sx = threadIdx.x % CW, sy = threadIdx.x / CW;
-  const int ox = blockIdx.x * CW + sx, oy = blockIdx.y * CH + sy;
+  const int ox = blockIdx.x * CW + sx, oy = by * CH + sy;
   if (f.p.flags & VRT_FLAG_RGB8_OUT) {
     // Packed RGB8: a patch row is CW*3 bytes = CW*3/4 words; thread sx composes word sx of the row from the patch bytes.
     constexpr int WPR = CW * 3 / 4;

@@ -144,8 +144,7 @@ struct DirConst {
   V3 d, inv;             // direction, 1/direction (+inf where d == 0)
   V3 tdel;               // time per cell (0 where d == 0)
   V3 off;                // 1 where d >= 0 else 0: the next plane of cell c is c + off
-  float invmax;          // 1 / max |d|
-  float jbias;           // (1 + 1/64) * invmax: a jump advances by r * invmax - jbias
+  float invmax;          // 1 / max |d|: time per cell of dominant-axis travel (a jump advances by (r - 1 - 1/64) * invmax)
   int dix, diy, diz;     // padded-index increment per axis step
   uint32_t ibias;        // constant folded into the jump's index computation (device path)
   int oct;               // direction octant: (d.x < 0) | (d.y < 0) << 1 | (d.z < 0) << 2 -> which cell array to walk
@@ -164,7 +163,6 @@ VRT_HD void set_dir_const(DirConst& w, const V3& d, int P) {
   w.off = mk3(d.x >= 0.0f ? 1.0f : 0.0f, d.y >= 0.0f ? 1.0f : 0.0f, d.z >= 0.0f ? 1.0f : 0.0f);
   // 1 / max|d| == min |1/d| exactly (correctly rounded reciprocals are monotone); zero components are +inf and drop out
   w.invmax = fminf(fabsf(w.inv.x), fminf(fabsf(w.inv.y), fabsf(w.inv.z)));
-  w.jbias = 1.015625f * w.invmax;
   w.dix = d.x > 0.0f ? 1 : -1;
   w.diy = d.y > 0.0f ? P : -P;
   w.diz = d.z > 0.0f ? P * P : -(P * P);

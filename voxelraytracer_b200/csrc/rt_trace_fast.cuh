@@ -94,22 +94,9 @@ struct FastTracer {
     if (sz) w.tmax.z += k.tdel.z;
   }
 
-  // Jump inside the empty box promised by radius r (r >= 2): advance by (r - 1 - 1/64) cells of dominant-axis
-  // travel, then re-derive the cell and the plane times from the position.  `tlim` is the largest float below the
-  // length cap: a jump that would pass the cap is shortened to land just before it (still inside the empty box), so
-  // that the steps the reference would still take from there - including the last one, which may overshoot the cap and
-  // hit (voxel.glsl:317-353) - are taken and tested one by one.  False only if that leaves no progress.
-  // After such a shortened jump `tlim` is set below every walk time, so the rest of the walk is plain steps (a second
-  // shortened jump could land on the same point again and, with plane times rounded behind it, never terminate).
-  static VRT_HD bool jump(Walk& w, const DirConst& k, uint32_t r, float& tlim, bool exits, int P, uint32_t ibias) {
-    // (float)r without a conversion instruction: 2^23 + r has r in its low mantissa bits
-    const float rf = u2f(0x4B000000u | r) - 8388608.0f;
-    float tn = fmaf(rf, k.invmax, w.t - k.jbias);
-    if (!(tn < tlim)) {
-      if (exits) { w.t = finf(); return false; }           // the empty box reaches past the chunk: the ray leaves it unobstructed
-      tn = tlim; tlim = -1.0f;
-    }
-    if (!(tn > w.t)) return false;
+  // Moves the walk to time tn (a point inside the current empty box): re-derives the cell and the plane times from the
+  // position, so no accumulated error survives a jump.
+  static VRT_HD void land(Walk& w, const DirConst& k, float tn, int P, uint32_t ibias) {
     const float qx = fmaf(tn, k.d.x, w.o.x), qy = fmaf(tn, k.d.y, w.o.y), qz = fmaf(tn, k.d.z, w.o.z);
 #if defined(__CUDA_ARCH__)
     // floor + float->int on the FMA/ALU pipes: add 1.5*2^23 rounding DOWN; the sum's low bits are floor(q)
@@ -117,6 +104,7 @@ struct FastTracer {
     const float fx = mx - 12582912.0f, fy = my - 12582912.0f, fz = mz - 12582912.0f;
     w.idx = (f2u(mz) * (uint32_t)P + f2u(my)) * (uint32_t)P + f2u(mx) - ibias;
 #else
+    (void)ibias;
     const float fx = floorf(qx), fy = floorf(qy), fz = floorf(qz);
     w.idx = (uint32_t)(((int)fz + 1) * P + ((int)fy + 1)) * (uint32_t)P + (uint32_t)((int)fx + 1);
 #endif
@@ -124,6 +112,31 @@ struct FastTracer {
     w.tmax.y = ((fy + k.off.y) - w.o.y) * k.inv.y;
     w.tmax.z = ((fz + k.off.z) - w.o.z) * k.inv.z;
     w.t = tn;
+  }
+
+  // Jump inside the empty box promised by radius r (r >= 2): advance by (r - 1 - 1/64) cells of dominant-axis travel.
+  // False if the walk has to step instead.  `tlim` = min(time the ray leaves the chunk, last float below the length
+  // cap).  A jump that would pass it is rare (once per walk at most) and handled out of line:
+  //  - tlim is the exit time: the empty box reaches past the chunk, the ray leaves it unobstructed (w.t = inf ends the walk);
+  //  - tlim is the cap: land on it - still inside the empty box - so that the steps the reference would still take from
+  //    there, including the last one, which may overshoot the cap and hit (voxel.glsl:317-353), are taken and tested
+  //    one by one.  After that tlim is set below every walk time: the rest of the walk is plain steps (a second
+  //    shortened jump could land on the same point again and, with plane times rounded behind it, never terminate).
+  static VRT_HD bool jump(Walk& w, const DirConst& k, uint32_t r, float& tlim, float tcapm, int P, uint32_t ibias) {
+    // (float)(r - 1) without a conversion instruction: 2^23 + r has r in its low mantissa bits; r - 1 - 1/64 is exact
+    const float rm = (u2f(0x4B000000u | r) - 8388609.0f) - 0.015625f;
+    const float tn = fmaf(rm, k.invmax, w.t);
+    if (__builtin_expect(!(tn < tlim), 0)) {
+      const float tl = tlim;
+      if (tl == -1.0f) return false;
+      if (tl < tcapm) { w.t = finf(); return false; }
+      tlim = -1.0f;
+      if (!(tl > w.t)) return false;
+      land(w, k, tl, P, ibias);
+      return true;
+    }
+    if (!(tn > w.t)) return false;
+    land(w, k, tn, P, ibias);                              // implies w.t < tn < tcap
     return true;
   }
 
@@ -135,16 +148,22 @@ struct FastTracer {
     if (r.face_axis >= 0) {
       // Spawned on a voxel face: the start cell is the one on the parent ray's side of the face, taken from
       // integers; if the new direction crosses the face, the crossing happens at t = 0.
-      float c[3] = {floorf(r.pos.x), floorf(r.pos.y), floorf(r.pos.z)};
+      // (Written with selects on the axis, not with arrays indexed by it: those would live in local memory.)
       const int a = r.face_axis;
-      float plane = rintf(vget(r.pos, a));
-      c[a] = r.face_nsign > 0.0f ? plane : plane - 1.0f;
-      for (int j = 0; j < 3; j++) c[j] = fminf(fmaxf(c[j], j == a ? -1.0f : 0.0f), j == a ? (float)n : fn1);
-      float da = vget(k.d, a);
-      bool into = da != 0.0f && (da > 0.0f) != (r.face_nsign > 0.0f);  // moving against the normal = through the face
-      if ((c[a] < 0.0f || c[a] > fn1) && !into) return false;          // on the chunk boundary, heading out
-      set_cell(w, k, c[0], c[1], c[2], P);
-      if (into) vset(w.tmax, a, 0.0f);
+      const bool ax = a == 0, ay = a == 1, az = !ax && !ay;
+      const float fnn = (float)n;
+      const float plane = rintf(ax ? r.pos.x : (ay ? r.pos.y : r.pos.z));
+      const float ca = r.face_nsign > 0.0f ? plane : plane - 1.0f;
+      // face axis: clamp to [-1, n] (the border cells); the others to [0, n-1]
+      const float cx = ax ? fminf(fmaxf(ca, -1.0f), fnn) : fminf(fmaxf(floorf(r.pos.x), 0.0f), fn1);
+      const float cy = ay ? fminf(fmaxf(ca, -1.0f), fnn) : fminf(fmaxf(floorf(r.pos.y), 0.0f), fn1);
+      const float cz = az ? fminf(fmaxf(ca, -1.0f), fnn) : fminf(fmaxf(floorf(r.pos.z), 0.0f), fn1);
+      const float da = ax ? k.d.x : (ay ? k.d.y : k.d.z);
+      const float cc = ax ? cx : (ay ? cy : cz);
+      const bool into = da != 0.0f && (da > 0.0f) != (r.face_nsign > 0.0f);  // moving against the normal = through the face
+      if ((cc < 0.0f || cc > fn1) && !into) return false;                    // on the chunk boundary, heading out
+      set_cell(w, k, cx, cy, cz, P);
+      if (into) { if (ax) w.tmax.x = 0.0f; else if (ay) w.tmax.y = 0.0f; else w.tmax.z = 0.0f; }
       w.t = 0.0f;
       return true;
     }
@@ -156,27 +175,23 @@ struct FastTracer {
     }
     // Outside: slab test; the walk starts in the border cell in front of the entry face so that the first
     // step crosses into the chunk and the entered cell is tested like any other.
-    float lo[3], hi[3];
-    for (int j = 0; j < 3; j++) {
-      float oj = vget(r.pos, j), dj = vget(k.d, j);
-      if (dj == 0.0f) {
-        if (oj < 0.0f || oj > fsize) return false;
-        lo[j] = -finf(); hi[j] = finf();
-      } else {
-        float ij = vget(k.inv, j);
-        float t0 = (0.0f - oj) * ij, t1 = (fsize - oj) * ij;
-        lo[j] = fminf(t0, t1); hi[j] = fmaxf(t0, t1);
-      }
-    }
-    float tin = fmaxf(lo[0], fmaxf(lo[1], lo[2])), tout = fminf(hi[0], fminf(hi[1], hi[2]));
+    // (per-axis scalars and selects: arrays indexed by the entry axis would live in local memory)
+    float lox, loy, loz, hix, hiy, hiz;
+    if (k.d.x == 0.0f) { if (r.pos.x < 0.0f || r.pos.x > fsize) return false; lox = -finf(); hix = finf(); }
+    else { const float t0 = (0.0f - r.pos.x) * k.inv.x, t1 = (fsize - r.pos.x) * k.inv.x; lox = fminf(t0, t1); hix = fmaxf(t0, t1); }
+    if (k.d.y == 0.0f) { if (r.pos.y < 0.0f || r.pos.y > fsize) return false; loy = -finf(); hiy = finf(); }
+    else { const float t0 = (0.0f - r.pos.y) * k.inv.y, t1 = (fsize - r.pos.y) * k.inv.y; loy = fminf(t0, t1); hiy = fmaxf(t0, t1); }
+    if (k.d.z == 0.0f) { if (r.pos.z < 0.0f || r.pos.z > fsize) return false; loz = -finf(); hiz = finf(); }
+    else { const float t0 = (0.0f - r.pos.z) * k.inv.z, t1 = (fsize - r.pos.z) * k.inv.z; loz = fminf(t0, t1); hiz = fmaxf(t0, t1); }
+    const float tin = fmaxf(lox, fmaxf(loy, loz)), tout = fminf(hix, fminf(hiy, hiz));
     if (!(tin < tout) || !(tout > 0.0f)) return false;
-    int ea = lo[0] >= lo[1] && lo[0] >= lo[2] ? 0 : (lo[1] >= lo[2] ? 1 : 2);
-    float q[3] = {r.pos.x + tin * k.d.x, r.pos.y + tin * k.d.y, r.pos.z + tin * k.d.z};
-    float c[3];
-    for (int j = 0; j < 3; j++) c[j] = fminf(fmaxf(floorf(q[j]), 0.0f), fn1);
-    c[ea] = vget(k.d, ea) > 0.0f ? -1.0f : (float)n;
-    set_cell(w, k, c[0], c[1], c[2], P);
-    vset(w.tmax, ea, tin);
+    const bool ex = lox >= loy && lox >= loz, ey = !ex && loy >= loz, ez = !ex && !ey;     // entry axis
+    const float fnn = (float)n;
+    const float cx = ex ? (k.d.x > 0.0f ? -1.0f : fnn) : fminf(fmaxf(floorf(r.pos.x + tin * k.d.x), 0.0f), fn1);
+    const float cy = ey ? (k.d.y > 0.0f ? -1.0f : fnn) : fminf(fmaxf(floorf(r.pos.y + tin * k.d.y), 0.0f), fn1);
+    const float cz = ez ? (k.d.z > 0.0f ? -1.0f : fnn) : fminf(fmaxf(floorf(r.pos.z + tin * k.d.z), 0.0f), fn1);
+    set_cell(w, k, cx, cy, cz, P);
+    if (ex) w.tmax.x = tin; else if (ey) w.tmax.y = tin; else w.tmax.z = tin;
     // entry time of the border cell = the latest plane crossing before tin (>= 0)
     float e0 = w.tmax.x - k.tdel.x, e1 = w.tmax.y - k.tdel.y, e2 = w.tmax.z - k.tdel.z;
     float te = fmaxf(0.0f, fmaxf(k.tdel.x == 0.0f ? 0.0f : e0, fmaxf(k.tdel.y == 0.0f ? 0.0f : e1, k.tdel.z == 0.0f ? 0.0f : e2)));
@@ -195,18 +210,17 @@ struct FastTracer {
   // This is the hot loop of the whole path: one 2-byte load per iteration, nothing else touches memory.
   static VRT_HD uint32_t walk_air(Ctx& cx, Walk& w, const DirConst& k, const uint16_t* cells, uint32_t rad, float tcap, int P) {
     if (!(tcap > 0.0f)) return 0xFFFFFFFFu;                // already at the length cap (w.t >= 0 always)
-    float tlim = u2f(f2u(tcap) - 1u);                      // next float below tcap
+    const float tcapm = u2f(f2u(tcap) - 1u);               // next float below tcap
     // The radius field looks through the chunk boundary (outside counts as empty), so a jump may aim past it: the time
     // at which the ray leaves the chunk bounds the jump instead.  Whichever of the two limits comes first decides what
     // passing it means: past the exit = the ray is gone; past the cap = land just before it and step (see jump).
     const float fs = cx.f.fsize;
     const float texit = fminf((k.off.x * fs - w.o.x) * k.inv.x, fminf((k.off.y * fs - w.o.y) * k.inv.y, (k.off.z * fs - w.o.z) * k.inv.z));
-    const bool exits = texit <= tlim;
-    if (exits) tlim = texit;
+    float tlim = fminf(texit, tcapm);
     for (;;) {
       VRT_HIST(rad);
       // a successful jump implies w.t < tn < tcap, so only the stepping path tests the cap itself
-      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tlim, exits, P, cx.f.ibias))) {
+      if (!(rad >= (uint32_t)VRT_JUMP_MIN && jump(w, k, rad, tlim, tcapm, P, cx.f.ibias))) {
         if (!(w.t < tcap)) return 0xFFFFFFFFu;
         // one step, or two for rad == 2, as a real (not if-converted) loop: predicated-off instructions of an unneeded
         // second step would still cost issue slots, and issue is the bound
