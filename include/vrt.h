@@ -163,6 +163,7 @@ int64_t vrt_kernel_launches(const vrt_ctx* ctx);
 typedef struct vrt_grid_info {
   int32_t size, pitch, radius_cap, octants;
   int64_t cells_total, voxels_occupied;
+  int64_t voxels_glass; /* voxels of material 2 (transparent + reflective); 0 lets the render skip all bounce-ray code */
 } vrt_grid_info;
 int vrt_grid_info_get(vrt_ctx* ctx, vrt_grid_info* out);
 int vrt_read_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count); /* count must be cells_total */

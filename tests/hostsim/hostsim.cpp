@@ -160,15 +160,20 @@ int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cel
   f.rows_local = (int)(vrt_tile_pixels(p) / p->tile_w);
   if (!finish_frame_args(f)) return -1;
   bool flat = (p->flags & VRT_FLAG_COLOR_ONLY) != 0;
+  const bool noisy = p->rayNoise != 0.0f || p->reflectionNoise != 0.0f || p->refractionNoise != 0.0f;
+  bool glass = false;                                      // any voxel of material 2 (what vrt_upload_grid counts)
+  { const size_t n3 = (size_t)p->size * p->size * p->size; for (size_t i = 0; i < n3 && !glass; i++) glass = grid[i] == 2; }
   uint64_t cnt[CNT_N] = {0};
   std::atomic<int> next(0);
   auto work = [&]() {
     if (mode == 0) {
       if (flat) render_rows<ExactTracer<true, true>, true>(f, next, out_f32, out_rgba8, out_hit, out_bounces, cnt);
       else render_rows<ExactTracer<false, true>, false>(f, next, out_f32, out_rgba8, out_hit, out_bounces, cnt);
-    } else {
-      if (flat) render_rows<FastTracer<true, true>, true>(f, next, out_f32, out_rgba8, out_hit, out_bounces, cnt);
-      else render_rows<FastTracer<false, true>, false>(f, next, out_f32, out_rgba8, out_hit, out_bounces, cnt);
+    } else {   // the instantiation the launcher would pick (launch_render, kernels.cu): NOISE from the uniforms, GLASS from the chunk
+#define HS_FAST(FL, NO, GL) render_rows<FastTracer<FL, true, NO, GL>, FL>(f, next, out_f32, out_rgba8, out_hit, out_bounces, cnt)
+      if (flat) { if (noisy) { if (glass) HS_FAST(true, true, true); else HS_FAST(true, true, false); } else { if (glass) HS_FAST(true, false, true); else HS_FAST(true, false, false); } }
+      else      { if (noisy) { if (glass) HS_FAST(false, true, true); else HS_FAST(false, true, false); } else { if (glass) HS_FAST(false, false, true); else HS_FAST(false, false, false); } }
+#undef HS_FAST
     }
   };
   if (nthreads < 1) nthreads = 1;

@@ -70,7 +70,7 @@ class Counters(C.Structure):
 
 class GridInfo(C.Structure):
     _fields_ = [("size", C.c_int32), ("pitch", C.c_int32), ("radius_cap", C.c_int32), ("octants", C.c_int32),
-                ("cells_total", C.c_int64), ("voxels_occupied", C.c_int64)]
+                ("cells_total", C.c_int64), ("voxels_occupied", C.c_int64), ("voxels_glass", C.c_int64)]
 
 
 def lib_path():

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) pack_cells(const uint8_t* __restrict__ gr
                                                    uint16_t* __restrict__ cells, int n, int log2n, int fwd, unsigned long long* stats) {
   const int P = n + 2;
   const size_t total = (size_t)P * P * P;
-  unsigned occupied = 0;
+  unsigned occupied = 0, glass = 0;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int x = (int)(i % P) - 1, y = (int)((i / P) % P) - 1, z = (int)(i / ((size_t)P * P)) - 1;
     uint16_t v = 0;
@@ -100,12 +100,15 @@ __global__ void __launch_bounds__(256) pack_cells(const uint8_t* __restrict__ gr
       }
       v = (uint16_t)((r << 8) | b);
       occupied += b ? 1u : 0u;
+      glass += b == 2u ? 1u : 0u;                          // material 2: the only transparent / reflective one (voxel.glsl:50-89)
     }
     cells[i] = v;
   }
   if (stats) {
     unsigned w = __reduce_add_sync(0xFFFFFFFFu, occupied);
     if ((threadIdx.x & 31) == 0 && w) atomicAdd(stats, (unsigned long long)w);
+    w = __reduce_add_sync(0xFFFFFFFFu, glass);
+    if ((threadIdx.x & 31) == 0 && w) atomicAdd(stats + 1, (unsigned long long)w);
   }
 }
 

@@ -9,15 +9,24 @@ namespace vrt {
 
 // LEAN selects the liberties only the fast traversal takes (hash skipped at zero noise, pow through ex2/lg2);
 // the exact traversal instantiates LEAN = false and stays a literal replay.
-template <bool FLAT, bool COUNT, bool LEAN = false>
+// NOISE = false (LEAN only) promises that all three noise uniforms are 0 - the reference's default (main.cpp:156-158) -
+// so the hash and the jittered-direction code are not even compiled in: same results as the run-time test, about a
+// quarter less code for the instruction cache.  The launcher picks it from the uniforms.
+// GLASS = false (LEAN only) promises that the chunk holds no voxel of material 2, the only transparent / reflective one
+// (voxel.glsl:50-89; counted at vrt_upload_grid): no bounce ray can exist, so the ray stack, the medium logic and the
+// reflection / refraction code are not compiled in.  Same results, a pixel is one march + at most one shadow ray.
+template <bool FLAT, bool COUNT, bool LEAN = false, bool NOISE = true, bool GLASS = true>
 struct PixelCtx {
   static constexpr bool kLean = LEAN;
+  static constexpr bool kNoise = NOISE;
+  static constexpr bool kGlass = GLASS;
   const FrameArgs& f;
   PixelCounters cnt;
   VRT_HD explicit PixelCtx(const FrameArgs& fa) : f(fa) { if (COUNT) cnt.clear(); }
   VRT_HD void count(int which, uint32_t n = 1) { if (COUNT) cnt.v[which] += n; }
 
   VRT_HD V3 jitter(V3 dir, V3 pos, float randomness) const {
+    if (LEAN && !NOISE) return normalize3_lean(dir);
     return LEAN ? randomize_direction_lean(dir, pos, randomness, f.p.time) : randomize_direction(dir, pos, randomness, f.p.time);
   }
   // pow(x, e) for x >= 0, e > 0.  LEAN on the device: ex2(e * lg2(x)) on the SFU (relative error ~ e * 2^-22, far
@@ -212,7 +221,7 @@ VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
   V3 vnear, vdir;
   // The hash behind u_RayNoise amplifies a last-ulp difference of its inputs (vnear, direction) into a different
   // random offset, so with primary-ray noise the fast traversal generates the ray with the pinned arithmetic too.
-  const bool lean_gen = Tracer::Ctx::kLean && p.rayNoise == 0.0f;
+  const bool lean_gen = Tracer::Ctx::kLean && (!Tracer::Ctx::kNoise || p.rayNoise == 0.0f);
   if (lean_gen) {   // reciprocal-multiply instead of three IEEE divisions each
     const float iw = 1.0f / nr[3], jw = 1.0f / fr[3];
     vnear = mk3(nr[0] * iw, nr[1] * iw, nr[2] * iw);
@@ -238,7 +247,7 @@ VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
     Hit h = trace_with_shadow<Tracer, FLAT>(cx, r, color);
     if (popped == 0 && h.found) out.hit = h.cell;
     popped++;
-    if (h.found) {
+    if (Tracer::Ctx::kGlass && h.found) {
       MatProps mt = material_of<FLAT>(h.voxel);
       if (mt.reflective && r.nrefl < p.maxReflections && n < kStack) stack[n++] = cx.reflection_of(r, h);
       if (mt.transparent && r.ntrans < p.maxTransparencies) {
@@ -247,7 +256,7 @@ VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
         if (c[3] != 1.0f && n < kStack) stack[n++] = cx.refraction_of(r, h);
       }
     }
-    if (n == 0) break;
+    if (!Tracer::Ctx::kGlass || n == 0) break;
     r = stack[--n];
   }
   out.rgba[0] = color.x; out.rgba[1] = color.y; out.rgba[2] = color.z; out.rgba[3] = 1.0f;

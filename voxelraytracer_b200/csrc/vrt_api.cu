@@ -162,14 +162,14 @@ static int repack_locked(vrt_ctx* ctx, int size, cudaStream_t s) {
   cudaFree(tmp);
   if (e != cudaSuccess || e2 != cudaSuccess)
     return fail(ctx, VRT_E_CUDA, "repack: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
-  unsigned long long occ = 0;
-  CU(cudaMemcpy(&occ, ctx->d_stats, sizeof(occ), cudaMemcpyDeviceToHost));
+  unsigned long long occ[2] = {0, 0};                      // [0] occupied voxels, [1] voxels of material 2 (glass)
+  CU(cudaMemcpy(occ, ctx->d_stats, sizeof(occ), cudaMemcpyDeviceToHost));
   ctx->size = size;
   ctx->octants = oct;
   ctx->log2n = 0;
   while ((1 << ctx->log2n) < size) ctx->log2n++;
   ctx->info.size = size; ctx->info.pitch = size + 2; ctx->info.radius_cap = cap; ctx->info.octants = oct ? 8 : 1;
-  ctx->info.cells_total = (int64_t)p3 * (oct ? 8 : 1); ctx->info.voxels_occupied = (int64_t)occ;
+  ctx->info.cells_total = (int64_t)p3 * (oct ? 8 : 1); ctx->info.voxels_occupied = (int64_t)occ[0]; ctx->info.voxels_glass = (int64_t)occ[1];
   return VRT_OK;
 }
 
@@ -306,7 +306,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   if ((p->flags & VRT_FLAG_PERSISTENT) && !debug && !(p->flags & (VRT_FLAG_EXACT | VRT_FLAG_RGB8_OUT))) {
     CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, (unsigned int*)(ctx->d_stats + 4), ctx->num_sms, s));
   } else {
-    CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, remote_target(ctx, d_out), s));
+    CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, remote_target(ctx, d_out), ctx->info.voxels_glass != 0, s));
   }
   CU(cudaEventRecord(ctx->ev1, s));
   ctx->launches += 1;
