@@ -123,7 +123,7 @@ static void render_rows(const FrameArgs& f, std::atomic<int>& next, float* out_f
   for (;;) {
     int ly = next.fetch_add(1);
     if (ly >= f.rows_local) break;
-    int py = frame_row(f.p, ly);
+    int py = frame_row(f, ly);
     for (int lx = 0; lx < f.p.tile_w; lx++) {
       typename Tracer::Ctx cx(f);
       PixelResult r = shade_pixel<Tracer, FLAT>(cx, f.p.tile_x0 + lx, py);

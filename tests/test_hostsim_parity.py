@@ -134,3 +134,16 @@ def test_randomised_poses_terminate_and_exact_replay_stays_bit_exact():
     assert line["hung_or_crashed"] == 0, r.stdout
     assert line["exact_not_bit_exact"] == 0, r.stdout
     assert line["mismatch_frac"] < 5e-4, r.stdout          # lattice-aligned cameras included (whole pixel lines on voxel edges)
+
+
+@pytest.mark.parametrize("world,band_rows", [(8, 16), (3, 4), (4, 7), (2, 1)])
+def test_band_rows_of_the_device_headers_stitch_to_the_full_frame(world, band_rows):
+    """frame_row() of rt_common.cuh (shift path for 2^k-row bands, division otherwise): every rank's compact rows are the rows
+    the sharding module says they are, so the bands stitch to the frame rendered in one piece."""
+    from voxelraytracer_b200 import sharding
+    grid, n, atlas, ts = scene("terrain32")
+    Wb, Hb = 96, 70
+    p = make_params(Wb, Hb, "terrain32", "terrain32_above")
+    full = hostsim_render(p, grid, atlas, 1).rgba8.reshape(Hb, Wb, 4)
+    parts = [hostsim_render(sharding.band_params(p, r, world, band_rows), grid, atlas, 1).rgba8.reshape(-1, Wb, 4) for r in range(world)]
+    assert np.array_equal(sharding.stitch_bands(parts, Hb, Wb, band_rows), full)

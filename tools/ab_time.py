@@ -9,6 +9,7 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 CASES = {"c2": ("terrain128", ["terrain_inside", "terrain_low", "terrain_above"], 1920, 1080, None),
          "c3": ("refraction128", ["refraction_close"], 1920, 1080, None),
          "c4": ("terrain128_glass", ["glass_wall", "terrain_inside"], 3840, 2160, None),
+         "c4b": ("terrain128_glass", ["glass_wall", "terrain_inside"], 3840, 2160, None),    # one rank's share of 8: 16-row bands, band 3
          "c5s": ("synthetic512", ["orbit0", "orbit21", "orbit42"], 3840, 2160, 1024.0)}
 
 
@@ -28,6 +29,10 @@ def worker(cases, reps):
         for pose in poses:
             pz = common.orbit_pose(int(pose[5:]), 64, 300.0, 125.0) if pose.startswith("orbit") else pose
             p = common.make_params(W, H, sc, pz, 0, max_len=max_len)
+            if name == "c4b":
+                from voxelraytracer_b200 import sharding
+                p = sharding.band_params(p, 3, 8, 16)
+                p.flags |= vrt.FLAG_OUT_FRAME
             t = []
             for i in range(reps + 5):
                 ctx.temporal_blend(fa, fb, nflush, 0.5)

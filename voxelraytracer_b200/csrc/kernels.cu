@@ -26,7 +26,7 @@ constexpr int kThreads = 128;                                      // 4 warps pe
 
 // Where pixel (lx, ly) of the tile goes in the colour target: compact tile rows, or its frame position (OUT_FRAME).
 __device__ __forceinline__ size_t colour_index(const FrameArgs& f, int lx, int ly) {
-  if (f.p.flags & VRT_FLAG_OUT_FRAME) return (size_t)frame_row(f.p, ly) * (size_t)f.p.width + (size_t)(f.p.tile_x0 + lx);
+  if (f.p.flags & VRT_FLAG_OUT_FRAME) return (size_t)frame_row(f, ly) * (size_t)f.p.width + (size_t)(f.p.tile_x0 + lx);
   return (size_t)ly * (size_t)f.p.tile_w + (size_t)lx;
 }
 
@@ -37,7 +37,7 @@ __device__ __forceinline__ void render_one(const FrameArgs& f, int lx, int ly, u
   typename Tracer::Ctx cx(f);
   const bool live = lx < f.p.tile_w && ly < f.rows_local;
   if (live) {
-    const int px = f.p.tile_x0 + lx, py = frame_row(f.p, ly);
+    const int px = f.p.tile_x0 + lx, py = frame_row(f, ly);
     PixelResult r = shade_pixel<Tracer, FLAT>(cx, px, py);
     const size_t o = (size_t)ly * (size_t)f.p.tile_w + (size_t)lx;                         // compact tile position
     uchar4 q;

@@ -194,6 +194,7 @@ struct FrameArgs {
   const uint16_t* sun_cells;  // cells + sun.oct * oct_stride: the array every shadow ray walks
   int rows_local;           // number of compact rows this launch writes
   int log2n;
+  int band_shift;           // log2(band_rows) when band_rows is a power of two (frame_row then needs no division), else -1
 };
 
 // Derived per-frame fields (host side, IEEE float ops: same bits as the device would compute).  p, the pointers
@@ -205,6 +206,9 @@ inline bool finish_frame_args(FrameArgs& a) {
   a.tex_scale = a.p.atlasSize > 0 ? (float)a.p.atlasTextureSize / (float)a.p.atlasSize : 0.0f;
   a.log2n = 0;
   while ((1 << a.log2n) < a.p.size) a.log2n++;
+  a.band_shift = -1;
+  if (a.p.band_count > 1 && a.p.band_rows > 0 && (a.p.band_rows & (a.p.band_rows - 1)) == 0)
+    for (a.band_shift = 0; (1 << a.band_shift) < a.p.band_rows;) a.band_shift++;
   set_dir_const(a.sun, a.sun_unit, a.p.size + 2);
   a.pitch = a.p.size + 2;
   a.ibias = a.sun.ibias;
@@ -218,6 +222,14 @@ VRT_HD int frame_row(const vrt_params& p, int ly) {
   int br = p.band_rows > 0 ? p.band_rows : 1;
   int lb = ly / br;
   return p.tile_y0 + (lb * p.band_count + p.band_index) * br + (ly - lb * br);
+}
+
+// The same through the frame's precomputed shift: two integer divisions less per pixel with the usual 2^k-row bands.
+VRT_HD int frame_row(const FrameArgs& f, int ly) {
+  if (f.p.band_count <= 1) return f.p.tile_y0 + ly;
+  if (f.band_shift < 0) return frame_row(f.p, ly);
+  const int lb = ly >> f.band_shift;
+  return f.p.tile_y0 + (((lb * f.p.band_count + f.p.band_index) << f.band_shift) + (ly & ((1 << f.band_shift) - 1)));
 }
 
 VRT_HD uint8_t quantize_unorm8(float c) {  // pin G6: round(clamp(c,0,1)*255); NaN -> 0

@@ -153,7 +153,8 @@ struct PixelCtx {
 
   // GetSkyboxColor (voxel.glsl:386-393) with pin G2
   VRT_HD V3 sky(const Ray& r, V3 color) const {
-    V3 u = LEAN ? normalize3_lean(r.dir) : normalize3(r.dir);
+    // LEAN: every ray direction is already unit length to the last ulps; renormalising moves the colour by ~1e-7
+    V3 u = LEAN ? r.dir : normalize3(r.dir);
     float d = dot3(f.sun_unit, u);
     float sun = d < 0.0f ? 0.0f : 10.0f * pow_pos(d, 400.0f);
     float grad = (u.y + 1.0f) * 0.5f;
