@@ -65,7 +65,10 @@ I_STEP = 16          # algorithmic thread-instructions per reference DDA step (S
 NCU_TRAFFIC = {"c2": 2.9e6, "c5": 3.4e9}   # dram read + write per launch: profiles/r01_ncu_c2_end.txt, r01_ncu_c5.txt
 # smsp__issue_active (share of issue slots really used, i.e. the fraction of the issue roofline without the credit for skipped
 # steps) and executed thread-instructions per launch from the same captures; static numbers from profiles/, not measured by this run
-NCU_ISSUE = {"c2": (0.850, "profiles/r01_ncu_c2_end.txt"), "c4": (0.844, "profiles/r01_ncu_c4.txt"), "c5": (0.777, "profiles/r01_ncu_c5.txt")}
+# (the C2 / C4 captures predate the kernel specialisations of profiles/r01_ab_specialisations.txt: traversal loop and data layout
+# are the same, the instruction count per pixel is lower now - to be re-captured with the next round's GPU budget)
+NCU_ISSUE = {"c2": (0.850, "profiles/r01_ncu_c2_end.txt (kernel build before the NOISE/GLASS specialisations)"),
+             "c4": (0.844, "profiles/r01_ncu_c4.txt (kernel build before the NOISE/GLASS specialisations)"), "c5": (0.777, "profiles/r01_ncu_c5.txt")}
 
 
 def parse():
