@@ -66,13 +66,20 @@ def test_fast_kernel_within_caps(ctx, sc, pose, flags, W, H):
 
 
 def test_plain_render_equals_debug_render(ctx):
-    """The non-debug kernel variants (the ones the bench times) write the same pixels as the instrumented ones."""
-    for sc, pose, fl in (("terrain128", "terrain_inside", 0), ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY), ("terrain128", "terrain_low", vrt.FLAG_EXACT)):
+    """The non-debug kernel variants (the ones the bench times) write the same pixels as the instrumented ones.  The timed fast
+    kernels are instantiations without the code a frame cannot reach (no noise uniforms -> no hash; no glass in the chunk -> no
+    bounce rays; kernels.cu launch_fast), the instrumented ones are generic: all four combinations are compared."""
+    noise = (0.01, 0.05, 0.02)
+    for sc, pose, fl, nz in (("terrain128", "terrain_inside", 0, None), ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY, None),
+                             ("terrain128", "terrain_low", vrt.FLAG_EXACT, None), ("terrain128", "terrain_above", 0, noise),
+                             ("refraction128", "refraction_close", 0, None), ("terrain128_glass", "glass_wall", 0, noise),
+                             ("terrain32", "terrain32_above", vrt.FLAG_COLOR_ONLY, None)):
         grid, n, atlas, ts = upload(ctx, sc)
-        p = make_params(640, 360, sc, pose, fl)
+        assert (ctx.grid_info().voxels_glass != 0) == bool((grid == 2).any())
+        p = make_params(640, 360, sc, pose, fl, noise=nz, time=3.0) if nz else make_params(640, 360, sc, pose, fl)
         a = gpu_render(ctx, p, flags_extra=0).rgba8
         b = gpu_render(ctx, p).rgba8
-        assert np.array_equal(a, b)
+        assert np.array_equal(a, b), (sc, pose, fl, nz)
 
 
 def test_repack_matches_host_statement(ctx):
@@ -86,6 +93,7 @@ def test_repack_matches_host_statement(ctx):
                 assert np.array_equal(ctx.read_cells(), hostsim_cells(grid, n, octants)), (sc, octants)
                 info = ctx.grid_info()
                 assert info.size == n and info.pitch == n + 2 and info.voxels_occupied == int((grid != 0).sum())
+                assert info.voxels_glass == int((grid == 2).sum())
                 assert info.octants == (8 if octants else 1) and info.cells_total == (8 if octants else 1) * (n + 2) ** 3
     finally:
         ctx.set_option(vrt.OPT_OCTANT_FIELDS, 1)
