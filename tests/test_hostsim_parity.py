@@ -147,3 +147,17 @@ def test_band_rows_of_the_device_headers_stitch_to_the_full_frame(world, band_ro
     full = hostsim_render(p, grid, atlas, 1).rgba8.reshape(Hb, Wb, 4)
     parts = [hostsim_render(sharding.band_params(p, r, world, band_rows), grid, atlas, 1).rgba8.reshape(-1, Wb, 4) for r in range(world)]
     assert np.array_equal(sharding.stitch_bands(parts, Hb, Wb, band_rows), full)
+
+
+def test_rays_in_the_far_boundary_plane_sample_the_wrapped_column():
+    """Pin G4 in the fast traversal: a camera placed exactly on the chunk's +x face sends a line of pixels along the plane
+    x == size with direction.x == 0; GetVoxel lets that coordinate through (voxel.glsl:151) and the REPEAT wrap reads column 0,
+    not the wall in column size-1 (found by tools/fuzz_hostsim.py, seed 20261105 case 46)."""
+    grid, n, atlas, ts = scene("terrain128")
+    p = make_params(64, 200, "terrain128", ((64.0, -8.103337157281956, 52.80251210739749), (0.8001285390172226, 2.9449588927211945, 0.0)), 0,
+                    time_of_day=42.711945995857704, max_len=400.0)
+    p.maxReflections, p.maxTransparencies = 2, 1
+    o = oracle_render(p, grid, atlas)
+    g = hostsim_render(p, grid, atlas, 1)
+    assert int(((g.hit != o.hit) | (g.bounces != o.bounces)).sum()) <= 1
+    assert (rms255(g.rgba8, o.rgba8) <= 1.0).all()

@@ -152,7 +152,16 @@ struct FastTracer {
     return true;
   }
 
-  // Start of a ray.  Returns false when the ray can never touch the chunk.
+  // Pin G4 for a ray that runs IN one of the chunk's far boundary planes (origin coordinate == size exactly, direction
+  // component exactly 0 - e.g. a line of pixels of a camera placed exactly on that face): GetVoxel lets coord == size
+  // through its bounds test (voxel.glsl:151) and the REPEAT wrap of the 3D texture (main.cpp:315-318) maps it to texel 0,
+  // so such a ray samples column 0 of that axis all the way, not the last column the clamp would give.
+  static VRT_HD void on_far_plane(float& cx, float& cy, float& cz, const V3& o, const V3& d, float fsize) {
+    if (o.x == fsize && d.x == 0.0f) cx = 0.0f;
+    if (o.y == fsize && d.y == 0.0f) cy = 0.0f;
+    if (o.z == fsize && d.z == 0.0f) cz = 0.0f;
+  }
+
   static VRT_HD bool begin(Walk& w, const DirConst& k, const Ray& r, float fsize, int n, int P) {
     w.o = r.pos;
     w.inc = 0;
@@ -181,7 +190,9 @@ struct FastTracer {
     }
     bool inside = r.pos.x >= 0.0f && r.pos.x <= fsize && r.pos.y >= 0.0f && r.pos.y <= fsize && r.pos.z >= 0.0f && r.pos.z <= fsize;
     if (inside) {
-      set_cell(w, k, fminf(floorf(r.pos.x), fn1), fminf(floorf(r.pos.y), fn1), fminf(floorf(r.pos.z), fn1), P);
+      float cx = fminf(floorf(r.pos.x), fn1), cy = fminf(floorf(r.pos.y), fn1), cz = fminf(floorf(r.pos.z), fn1);
+      if (__builtin_expect(r.pos.x == fsize || r.pos.y == fsize || r.pos.z == fsize, 0)) on_far_plane(cx, cy, cz, r.pos, k.d, fsize);
+      set_cell(w, k, cx, cy, cz, P);
       w.t = 0.0f;
       return true;
     }
@@ -202,7 +213,9 @@ struct FastTracer {
     const float cx = ex ? (k.d.x > 0.0f ? -1.0f : fnn) : fminf(fmaxf(floorf(r.pos.x + tin * k.d.x), 0.0f), fn1);
     const float cy = ey ? (k.d.y > 0.0f ? -1.0f : fnn) : fminf(fmaxf(floorf(r.pos.y + tin * k.d.y), 0.0f), fn1);
     const float cz = ez ? (k.d.z > 0.0f ? -1.0f : fnn) : fminf(fmaxf(floorf(r.pos.z + tin * k.d.z), 0.0f), fn1);
-    set_cell(w, k, cx, cy, cz, P);
+    float cx2 = cx, cy2 = cy, cz2 = cz;
+    if (__builtin_expect(r.pos.x == fsize || r.pos.y == fsize || r.pos.z == fsize, 0)) on_far_plane(cx2, cy2, cz2, r.pos, k.d, fsize);
+    set_cell(w, k, cx2, cy2, cz2, P);
     if (ex) w.tmax.x = tin; else if (ey) w.tmax.y = tin; else w.tmax.z = tin;
     // entry time of the border cell = the latest plane crossing before tin (>= 0)
     float e0 = w.tmax.x - k.tdel.x, e1 = w.tmax.y - k.tdel.y, e2 = w.tmax.z - k.tdel.z;
