@@ -195,6 +195,8 @@ struct FrameArgs {
   int rows_local;           // number of compact rows this launch writes
   int log2n;
   int band_shift;           // log2(band_rows) when band_rows is a power of two (frame_row then needs no division), else -1
+  int w_const;              // u_PVInvMatrix maps every pixel to the same clip w at the near and at the far plane (any perspective x rigid view)
+  float inv_w_near, inv_w_far;   // then: 1 / that w (fast traversal's ray generation; see shade_pixel)
 };
 
 // Derived per-frame fields (host side, IEEE float ops: same bits as the device would compute).  p, the pointers
@@ -206,6 +208,14 @@ inline bool finish_frame_args(FrameArgs& a) {
   a.tex_scale = a.p.atlasSize > 0 ? (float)a.p.atlasTextureSize / (float)a.p.atlasSize : 0.0f;
   a.log2n = 0;
   while ((1 << a.log2n) < a.p.size) a.log2n++;
+  // Row 3 of the matrix is (0, 0, c, d) for the inverse of perspective x rigid view (src/main.cpp:69,75,161): the unprojected
+  // w of a pixel does not depend on the pixel, so its reciprocal is a per-frame constant.  Same operations as shade_pixel.
+  a.w_const = a.p.invPV[3] == 0.0f && a.p.invPV[7] == 0.0f;
+  {
+    const float xy = a.p.invPV[3] * 0.0f + a.p.invPV[7] * 0.0f;
+    a.inv_w_near = 1.0f / ((xy + a.p.invPV[11] * -1.0f) + a.p.invPV[15] * 1.0f);
+    a.inv_w_far = 1.0f / ((xy + a.p.invPV[11] * 1.0f) + a.p.invPV[15] * 1.0f);
+  }
   a.band_shift = -1;
   if (a.p.band_count > 1 && a.p.band_rows > 0 && (a.p.band_rows & (a.p.band_rows - 1)) == 0)
     for (a.band_shift = 0; (1 << a.band_shift) < a.p.band_rows;) a.band_shift++;

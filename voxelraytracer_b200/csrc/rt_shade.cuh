@@ -224,7 +224,9 @@ VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
   // random offset, so with primary-ray noise the fast traversal generates the ray with the pinned arithmetic too.
   const bool lean_gen = Tracer::Ctx::kLean && (!Tracer::Ctx::kNoise || p.rayNoise == 0.0f);
   if (lean_gen) {   // reciprocal-multiply instead of three IEEE divisions each
-    const float iw = 1.0f / nr[3], jw = 1.0f / fr[3];
+    float iw, jw;
+    if (cx.f.w_const) { iw = cx.f.inv_w_near; jw = cx.f.inv_w_far; }   // the same two IEEE reciprocals, taken once per frame on the host
+    else { iw = 1.0f / nr[3]; jw = 1.0f / fr[3]; }
     vnear = mk3(nr[0] * iw, nr[1] * iw, nr[2] * iw);
     vdir = mk3(fr[0] * jw - vnear.x, fr[1] * jw - vnear.y, fr[2] * jw - vnear.z);
   } else {
