@@ -197,7 +197,18 @@ struct FrameArgs {
   int band_shift;           // log2(band_rows) when band_rows is a power of two (frame_row then needs no division), else -1
   int w_const;              // u_PVInvMatrix maps every pixel to the same clip w at the near and at the far plane (any perspective x rigid view)
   float inv_w_near, inv_w_far;   // then: 1 / that w (fast traversal's ray generation; see shade_pixel)
+  int ndc_by_rcp;           // (px + 0.5) / width and (py + 0.5) / height equal the reciprocal-multiply-correct form below for EVERY pixel
+  float rcp_width, rcp_height;   //   of this frame size (checked exhaustively on the host): RN(1 / width), RN(1 / height)
 };
+
+// a / b through a correctly rounded reciprocal y = RN(1 / b): q = RN(a y), r = a - b q (exact in the FMA), RN(q + r y).
+// Equals the IEEE quotient RN(a / b) for all but special b (Markstein); finish_frame_args does not rely on the theorem but
+// compares it with the division for every pixel coordinate of the frame before the kernel is allowed to use it.
+VRT_HD float div_by_rcp(float a, float b, float y) {
+  const float q = a * y;
+  const float r = fmaf(-q, b, a);
+  return fmaf(r, y, q);
+}
 
 // Derived per-frame fields (host side, IEEE float ops: same bits as the device would compute).  p, the pointers
 // and rows_local must be set by the caller.  Returns false if p.size is not a power of two.
@@ -215,6 +226,19 @@ inline bool finish_frame_args(FrameArgs& a) {
     const float xy = a.p.invPV[3] * 0.0f + a.p.invPV[7] * 0.0f;
     a.inv_w_near = 1.0f / ((xy + a.p.invPV[11] * -1.0f) + a.p.invPV[15] * 1.0f);
     a.inv_w_far = 1.0f / ((xy + a.p.invPV[11] * 1.0f) + a.p.invPV[15] * 1.0f);
+  }
+  {
+    // frame sizes repeat from call to call: remember the verdict of the last size checked
+    static thread_local int cw = 0, ch = 0, cok = 0;
+    a.rcp_width = 1.0f / (float)a.p.width;
+    a.rcp_height = 1.0f / (float)a.p.height;
+    if (cw != a.p.width || ch != a.p.height) {
+      bool ok = a.p.width > 0 && a.p.height > 0;
+      for (int x = 0; ok && x < a.p.width; x++) ok = div_by_rcp((float)x + 0.5f, (float)a.p.width, a.rcp_width) == ((float)x + 0.5f) / (float)a.p.width;
+      for (int y = 0; ok && y < a.p.height; y++) ok = div_by_rcp((float)y + 0.5f, (float)a.p.height, a.rcp_height) == ((float)y + 0.5f) / (float)a.p.height;
+      cw = a.p.width; ch = a.p.height; cok = ok ? 1 : 0;
+    }
+    a.ndc_by_rcp = cok;
   }
   a.band_shift = -1;
   if (a.p.band_count > 1 && a.p.band_rows > 0 && (a.p.band_rows & (a.p.band_rows - 1)) == 0)

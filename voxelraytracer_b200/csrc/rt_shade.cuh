@@ -208,10 +208,16 @@ template <class Tracer, bool FLAT>
 VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
   const vrt_params& p = cx.f.p;
   const float* m = p.invPV;
-  // kept as IEEE divisions in both traversals: a 1-ulp error in the NDC coordinate measurably raises the number of
-  // grazing-ray mismatches against the oracle (tools/parity_report.py), unlike the reciprocals further down
-  float nx = ((float)px + 0.5f) / (float)p.width * 2.0f - 1.0f;
-  float ny = ((float)py + 0.5f) / (float)p.height * 2.0f - 1.0f;
+  // The NDC coordinates keep the bits of the IEEE divisions in both traversals: a 1-ulp error in them measurably raises the
+  // number of grazing-ray mismatches against the oracle (tools/parity_report.py), unlike the reciprocals further down.
+  float nx, ny;
+  if (Tracer::Ctx::kLean && cx.f.ndc_by_rcp) {   // the same quotients without the division sequence (verified per frame size on the host)
+    nx = div_by_rcp((float)px + 0.5f, (float)p.width, cx.f.rcp_width) * 2.0f - 1.0f;
+    ny = div_by_rcp((float)py + 0.5f, (float)p.height, cx.f.rcp_height) * 2.0f - 1.0f;
+  } else {
+    nx = ((float)px + 0.5f) / (float)p.width * 2.0f - 1.0f;
+    ny = ((float)py + 0.5f) / (float)p.height * 2.0f - 1.0f;
+  }
   float nr[4], fr[4];
 #pragma unroll
   for (int i = 0; i < 4; i++) {
