@@ -161,3 +161,16 @@ def test_rays_in_the_far_boundary_plane_sample_the_wrapped_column():
     g = hostsim_render(p, grid, atlas, 1)
     assert int(((g.hit != o.hit) | (g.bounces != o.bounces)).sum()) <= 1
     assert (rms255(g.rgba8, o.rgba8) <= 1.0).all()
+
+
+def test_camera_on_a_lattice_point_starts_in_the_cell_it_moves_into():
+    """A camera on integer coordinates with an axis-aligned view: whole lines of pixels start exactly on a lattice plane.  The
+    reference counts a ray moving in the negative direction as being in the cell below the plane already (nextPlane =
+    ceil(pos - 1), voxel.glsl:306-309), so that cell is never tested (tools/fuzz_hostsim.py, seed 2 case 5: 61 px before)."""
+    grid, n, atlas, ts = scene("terrain128_glass")
+    p = make_params(97, 61, "terrain128_glass", ((-39.0, -42.0, -41.0), (1.5692255304681018, 3.141592653589793, 0.0)), 0,
+                    time_of_day=24.424928654198467)
+    p.maxReflections, p.maxTransparencies = 0, 1
+    o = oracle_render(p, grid, atlas)
+    g = hostsim_render(p, grid, atlas, 1)
+    assert int(((g.hit != o.hit) | (g.bounces != o.bounces)).sum()) <= 1

@@ -152,14 +152,18 @@ struct FastTracer {
     return true;
   }
 
-  // Pin G4 for a ray that runs IN one of the chunk's far boundary planes (origin coordinate == size exactly, direction
-  // component exactly 0 - e.g. a line of pixels of a camera placed exactly on that face): GetVoxel lets coord == size
-  // through its bounds test (voxel.glsl:151) and the REPEAT wrap of the 3D texture (main.cpp:315-318) maps it to texel 0,
-  // so such a ray samples column 0 of that axis all the way, not the last column the clamp would give.
-  static VRT_HD void on_far_plane(float& cx, float& cy, float& cz, const V3& o, const V3& d, float fsize) {
-    if (o.x == fsize && d.x == 0.0f) cx = 0.0f;
-    if (o.y == fsize && d.y == 0.0f) cy = 0.0f;
-    if (o.z == fsize && d.z == 0.0f) cz = 0.0f;
+  // Start cell of a ray whose origin lies exactly ON a lattice plane of some axis (a camera placed on integer coordinates, or
+  // on a face of the chunk).  Rare, so handled out of line; per such axis:
+  //  - direction component < 0: the ray is moving into the cell below the plane, and the reference's DDA counts it as being
+  //    in that cell already (its next plane is ceil(pos - 1), voxel.glsl:306-309), so that cell is the untested start cell -
+  //    not floor(pos), from which a crossing at t = 0 would test it;
+  //  - direction component == 0 on the far boundary plane (coordinate == size): GetVoxel lets coord == size through its
+  //    bounds test (voxel.glsl:151) and the REPEAT wrap of the 3D texture (main.cpp:315-318) maps it to texel 0, so the ray
+  //    samples column 0 of that axis all the way, not the last column the clamp would give (pin G4).
+  static VRT_HD void on_lattice_plane(float& cx, float& cy, float& cz, const V3& o, const V3& d, float fsize) {
+    if (o.x == floorf(o.x)) { if (d.x < 0.0f) cx = o.x - 1.0f; else if (d.x == 0.0f && o.x == fsize) cx = 0.0f; }
+    if (o.y == floorf(o.y)) { if (d.y < 0.0f) cy = o.y - 1.0f; else if (d.y == 0.0f && o.y == fsize) cy = 0.0f; }
+    if (o.z == floorf(o.z)) { if (d.z < 0.0f) cz = o.z - 1.0f; else if (d.z == 0.0f && o.z == fsize) cz = 0.0f; }
   }
 
   static VRT_HD bool begin(Walk& w, const DirConst& k, const Ray& r, float fsize, int n, int P) {
@@ -190,8 +194,9 @@ struct FastTracer {
     }
     bool inside = r.pos.x >= 0.0f && r.pos.x <= fsize && r.pos.y >= 0.0f && r.pos.y <= fsize && r.pos.z >= 0.0f && r.pos.z <= fsize;
     if (inside) {
-      float cx = fminf(floorf(r.pos.x), fn1), cy = fminf(floorf(r.pos.y), fn1), cz = fminf(floorf(r.pos.z), fn1);
-      if (__builtin_expect(r.pos.x == fsize || r.pos.y == fsize || r.pos.z == fsize, 0)) on_far_plane(cx, cy, cz, r.pos, k.d, fsize);
+      const float fx = floorf(r.pos.x), fy = floorf(r.pos.y), fz = floorf(r.pos.z);
+      float cx = fminf(fx, fn1), cy = fminf(fy, fn1), cz = fminf(fz, fn1);
+      if (__builtin_expect(r.pos.x == fx || r.pos.y == fy || r.pos.z == fz, 0)) on_lattice_plane(cx, cy, cz, r.pos, k.d, fsize);
       set_cell(w, k, cx, cy, cz, P);
       w.t = 0.0f;
       return true;
@@ -214,7 +219,11 @@ struct FastTracer {
     const float cy = ey ? (k.d.y > 0.0f ? -1.0f : fnn) : fminf(fmaxf(floorf(r.pos.y + tin * k.d.y), 0.0f), fn1);
     const float cz = ez ? (k.d.z > 0.0f ? -1.0f : fnn) : fminf(fmaxf(floorf(r.pos.z + tin * k.d.z), 0.0f), fn1);
     float cx2 = cx, cy2 = cy, cz2 = cz;
-    if (__builtin_expect(r.pos.x == fsize || r.pos.y == fsize || r.pos.z == fsize, 0)) on_far_plane(cx2, cy2, cz2, r.pos, k.d, fsize);
+    if (__builtin_expect(r.pos.x == fsize || r.pos.y == fsize || r.pos.z == fsize, 0)) {   // pin G4, see on_lattice_plane
+      if (r.pos.x == fsize && k.d.x == 0.0f) cx2 = 0.0f;
+      if (r.pos.y == fsize && k.d.y == 0.0f) cy2 = 0.0f;
+      if (r.pos.z == fsize && k.d.z == 0.0f) cz2 = 0.0f;
+    }
     set_cell(w, k, cx2, cy2, cz2, P);
     if (ex) w.tmax.x = tin; else if (ey) w.tmax.y = tin; else w.tmax.z = tin;
     // entry time of the border cell = the latest plane crossing before tin (>= 0)
