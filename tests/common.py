@@ -185,22 +185,35 @@ def gpu_render(ctx, p, flags_extra=vrt.FLAG_DEBUG_MAPS | vrt.FLAG_FLOAT_OUT | vr
 _scene_cache = {}
 
 
+_atlas_cache = {}
+
+
+def ref_atlas(ts):
+    """The reference's own tiles (res/textures/{stone,dirt,glass,grass}[128].png, decoded once by tests/golden/make_tiles.py into
+    tests/golden/ref_tiles.npz) packed in AddTexture order (main.cpp:179-182,189-192) through vrt_atlas_pack.  ts = 16 or 128."""
+    if ts not in _atlas_cache:
+        t = np.load(os.path.join(ROOT, "tests", "golden", "ref_tiles.npz"))
+        _atlas_cache[ts] = vrt.atlas_pack(*[t["%s%d" % (n, ts)] for n in ("stone", "dirt", "glass", "grass")])
+    return _atlas_cache[ts]
+
+
 def scene(name):
-    """Returns (grid uint8[n^3], n, atlas uint8[as,as,4], texture_size)."""
+    """Returns (grid uint8[n^3], n, atlas uint8[as,as,4], texture_size).  C1-C4 scenes carry the reference's texture tiles; the
+    synthetic C5 family keeps the procedural atlas."""
     if name in _scene_cache:
         return _scene_cache[name]
     if name == "glass_cube32":       # C1 (main.cpp:259-271), _HIGH_PERFORMANCE sizes (main.cpp:177,184)
-        r = (vrt.scene_fill("glass_cube", 32), 32, vrt.atlas_synthetic(16), 16)
+        r = (vrt.scene_fill("glass_cube", 32), 32, ref_atlas(16), 16)
     elif name == "terrain32":        # _TERRAIN + _HIGH_PERFORMANCE: has the glass walls (size <= 64)
-        r = (vrt.scene_fill("terrain", 32), 32, vrt.atlas_synthetic(16), 16)
+        r = (vrt.scene_fill("terrain", 32), 32, ref_atlas(16), 16)
     elif name == "terrain128":       # C2
-        r = (vrt.scene_fill("terrain", 128), 128, vrt.atlas_synthetic(128), 128)
+        r = (vrt.scene_fill("terrain", 128), 128, ref_atlas(128), 128)
     elif name == "terrain128_glass":  # C4: guard at main.cpp:233 lifted
-        r = (vrt.scene_fill("terrain", 128, glass_walls=True), 128, vrt.atlas_synthetic(128), 128)
+        r = (vrt.scene_fill("terrain", 128, glass_walls=True), 128, ref_atlas(128), 128)
     elif name == "refraction128":    # C3 (main.cpp:272-288)
-        r = (vrt.scene_fill("refraction", 128), 128, vrt.atlas_synthetic(128), 128)
+        r = (vrt.scene_fill("refraction", 128), 128, ref_atlas(128), 128)
     elif name == "refraction32":
-        r = (vrt.scene_fill("refraction", 32), 32, vrt.atlas_synthetic(16), 16)
+        r = (vrt.scene_fill("refraction", 32), 32, ref_atlas(16), 16)
     elif name.startswith("synthetic"):  # C5 family: synthetic256 / synthetic512 / synthetic1024
         sz = int(name[len("synthetic"):])
         r = (vrt.scene_fill("synthetic", sz, seed=7), sz, vrt.atlas_synthetic(128), 128)

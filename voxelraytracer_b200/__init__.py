@@ -31,6 +31,7 @@ from .api import (  # noqa: F401
     camera_invpv,
     default_params,
     lib_path,
+    load_host_library,
     load_library,
     noise_heightmap,
     scene_fill,

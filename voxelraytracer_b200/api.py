@@ -91,9 +91,18 @@ def load_library():
         raise ImportError("libvrt.so is not built (%s missing); run `make -C voxelraytracer_b200/csrc` or "
                           "__graft_entry__.build().  There is no CPU fallback." % path)
     lib = C.CDLL(path)
+    for name, (res, args) in _signatures().items():
+        fn = getattr(lib, name)  # AttributeError here == header/library mismatch
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _signatures():
     vp, i32, i64, u32, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_float
     PP = C.POINTER(Params)
-    sig = {
+    return {
         "vrt_default_params": (None, [PP, i32, i32, i32]),
         "vrt_abi_version": (i32, []),
         "vrt_create": (i32, [i32, C.POINTER(vp)]),
@@ -139,11 +148,29 @@ def load_library():
         "vrt_sun_dir": (i32, [f32, f32, C.POINTER(f32)]),
         "vrt_write_png": (i32, [C.c_char_p, vp, i32, i32, i32]),
     }
-    for name, (res, args) in sig.items():
-        fn = getattr(lib, name)  # AttributeError here == header/library mismatch
-        fn.restype = res
-        fn.argtypes = args
-    _lib = lib
+
+
+# The CUDA-free part of the ABI (host_scene.cpp), also built as libvrt_host.so: scenes, atlas, camera, sun, PNG, default params.
+HOST_EXPORTS = ["vrt_default_params", "vrt_abi_version", "vrt_tile_pixels", "vrt_scene_fill", "vrt_noise_heightmap", "vrt_atlas_synthetic",
+                "vrt_atlas_pack", "vrt_camera_invpv", "vrt_sun_dir", "vrt_write_png"]
+_host_lib = None
+
+
+def load_host_library():
+    """libvrt_host.so: the host-side helpers only, no CUDA code mapped (CPU-only tooling: oracle drivers, bench.py --impl reference).
+    Same functions, same object file as the ones libvrt.so exports."""
+    global _host_lib
+    if _host_lib is not None:
+        return _host_lib
+    path = os.path.join(os.path.dirname(lib_path()), "libvrt_host.so")
+    if not os.path.exists(path):
+        raise ImportError("libvrt_host.so is not built (%s missing); run `make -C voxelraytracer_b200/csrc`" % path)
+    lib = C.CDLL(path)
+    full = _signatures()
+    for name in HOST_EXPORTS:
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = full[name]
+    _host_lib = lib
     return lib
 
 
@@ -153,23 +180,23 @@ def _ptr(a):
 
 def _host_check(rc, what):
     if rc != 0:
-        raise VrtError(rc, "%s: %s" % (what, load_library().vrt_last_error(None).decode()))
+        raise VrtError(rc, "%s failed (bad argument)" % what)
 
 
 # ---------------------------------------------------------------- host helpers (no GPU needed)
 def default_params(width, height, size):
     p = Params()
-    load_library().vrt_default_params(C.byref(p), width, height, size)
+    load_host_library().vrt_default_params(C.byref(p), width, height, size)
     return p
 
 
 def tile_pixels(p):
-    return int(load_library().vrt_tile_pixels(C.byref(p)))
+    return int(load_host_library().vrt_tile_pixels(C.byref(p)))
 
 
 def noise_heightmap(size, seed=1, octaves=5, persistence=0.125):
     out = np.zeros((size, size), np.float32)
-    _host_check(load_library().vrt_noise_heightmap(size, seed, octaves, persistence, _ptr(out)), "vrt_noise_heightmap")
+    _host_check(load_host_library().vrt_noise_heightmap(size, seed, octaves, persistence, _ptr(out)), "vrt_noise_heightmap")
     return out
 
 
@@ -181,13 +208,13 @@ def scene_fill(kind, size, heightmap=None, glass_walls=False, seed=1):
         heightmap = noise_heightmap(size, seed, 5, 0.5 if size <= 32 else 0.125)  # main.cpp:185,195
     out = np.zeros(size ** 3, np.uint8)
     hm = _ptr(np.ascontiguousarray(heightmap, np.float32)) if heightmap is not None else None
-    _host_check(load_library().vrt_scene_fill(kind, size, hm, 1 if glass_walls else 0, seed, _ptr(out)), "vrt_scene_fill")
+    _host_check(load_host_library().vrt_scene_fill(kind, size, hm, 1 if glass_walls else 0, seed, _ptr(out)), "vrt_scene_fill")
     return out
 
 
 def atlas_synthetic(texture_size=128, seed=7):
     out = np.zeros((2 * texture_size, 2 * texture_size, 4), np.uint8)
-    _host_check(load_library().vrt_atlas_synthetic(texture_size, seed, _ptr(out)), "vrt_atlas_synthetic")
+    _host_check(load_host_library().vrt_atlas_synthetic(texture_size, seed, _ptr(out)), "vrt_atlas_synthetic")
     return out
 
 
@@ -197,7 +224,7 @@ def atlas_pack(stone, dirt, glass, grass):
     for t in tiles:
         assert t.shape == (ts, ts, 4)
     out = np.zeros((2 * ts, 2 * ts, 4), np.uint8)
-    _host_check(load_library().vrt_atlas_pack(_ptr(tiles[0]), _ptr(tiles[1]), _ptr(tiles[2]), _ptr(tiles[3]), ts, _ptr(out)),
+    _host_check(load_host_library().vrt_atlas_pack(_ptr(tiles[0]), _ptr(tiles[1]), _ptr(tiles[2]), _ptr(tiles[3]), ts, _ptr(out)),
                 "vrt_atlas_pack")
     return out
 
@@ -205,7 +232,7 @@ def atlas_pack(stone, dirt, glass, grass):
 def camera_invpv(pos, rot, aspect, fov_deg=90.0, z_near=0.01, z_far=100.0):
     """Cam (src/main.cpp:14-77): rot in radians; returns float32[16], column-major."""
     out = (C.c_float * 16)()
-    _host_check(load_library().vrt_camera_invpv((C.c_float * 3)(*pos), (C.c_float * 3)(*rot), aspect, fov_deg, z_near, z_far, out),
+    _host_check(load_host_library().vrt_camera_invpv((C.c_float * 3)(*pos), (C.c_float * 3)(*rot), aspect, fov_deg, z_near, z_far, out),
                 "vrt_camera_invpv")
     return np.array(out, np.float32)
 
@@ -213,12 +240,12 @@ def camera_invpv(pos, rot, aspect, fov_deg=90.0, z_near=0.01, z_far=100.0):
 def write_png(path, rgba8, width, height, gl_row_order=True):
     """RGBA8 frame (as the render calls return it) -> 8-bit RGB PNG."""
     a = np.ascontiguousarray(rgba8, np.uint8).reshape(height, width, 4)
-    _host_check(load_library().vrt_write_png(str(path).encode(), _ptr(a), width, height, 1 if gl_row_order else 0), "vrt_write_png")
+    _host_check(load_host_library().vrt_write_png(str(path).encode(), _ptr(a), width, height, 1 if gl_row_order else 0), "vrt_write_png")
 
 
 def sun_dir(time_of_day=0.0, day_time=50.0):
     out = (C.c_float * 3)()
-    _host_check(load_library().vrt_sun_dir(time_of_day, day_time, out), "vrt_sun_dir")
+    _host_check(load_host_library().vrt_sun_dir(time_of_day, day_time, out), "vrt_sun_dir")
     return np.array(out, np.float32)
 
 

@@ -239,15 +239,15 @@ int vrt_camera_invpv(const float pos[3], const float rot[3], float aspect, float
 // ---- frame export (the reference's only file output is Utils::Screenshot, main.cpp:423-429) ----
 // Minimal PNG writer: 8-bit RGB, filter 0 on every scanline, zlib stream of stored (uncompressed) deflate blocks.
 namespace {
-uint32_t crc_table_entry(uint32_t n) { for (int k = 0; k < 8; k++) n = (n & 1u) ? 0xEDB88320u ^ (n >> 1) : n >> 1; return n; }
-uint32_t crc32_update(uint32_t c, const uint8_t* p, size_t n) {
+static uint32_t crc_table_entry(uint32_t n) { for (int k = 0; k < 8; k++) n = (n & 1u) ? 0xEDB88320u ^ (n >> 1) : n >> 1; return n; }
+static uint32_t crc32_update(uint32_t c, const uint8_t* p, size_t n) {
   static uint32_t table[256]; static bool init = false;
   if (!init) { for (uint32_t i = 0; i < 256; i++) table[i] = crc_table_entry(i); init = true; }
   for (size_t i = 0; i < n; i++) c = table[(c ^ p[i]) & 0xFFu] ^ (c >> 8);
   return c;
 }
-void put32(std::vector<uint8_t>& v, uint32_t x) { v.push_back(x >> 24); v.push_back(x >> 16); v.push_back(x >> 8); v.push_back(x); }
-void chunk(std::vector<uint8_t>& out, const char type[4], const std::vector<uint8_t>& data) {
+static void put32(std::vector<uint8_t>& v, uint32_t x) { v.push_back(x >> 24); v.push_back(x >> 16); v.push_back(x >> 8); v.push_back(x); }
+static void chunk(std::vector<uint8_t>& out, const char type[4], const std::vector<uint8_t>& data) {
   put32(out, (uint32_t)data.size());
   std::vector<uint8_t> td(type, type + 4);
   td.insert(td.end(), data.begin(), data.end());
