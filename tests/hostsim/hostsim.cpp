@@ -160,7 +160,7 @@ int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cel
   f.rows_local = (int)(vrt_tile_pixels(p) / p->tile_w);
   if (!finish_frame_args(f)) return -1;
   bool flat = (p->flags & VRT_FLAG_COLOR_ONLY) != 0;
-  const bool noisy = p->rayNoise != 0.0f || p->reflectionNoise != 0.0f || p->refractionNoise != 0.0f;
+  const bool noisy = f.careful != 0;                       // what launch_render looks at (kernels.cu)
   bool glass = false;                                      // any voxel of material 2 (what vrt_upload_grid counts)
   { const size_t n3 = (size_t)p->size * p->size * p->size; for (size_t i = 0; i < n3 && !glass; i++) glass = grid[i] == 2; }
   uint64_t cnt[CNT_N] = {0};

@@ -144,9 +144,14 @@ static cudaError_t launch_variant_persistent(const FrameArgs& a, unsigned int* t
   return cudaGetLastError();
 }
 
-cudaError_t launch_render_persistent(const FrameArgs& a, bool flat, unsigned int* ticket, int num_sms, cudaStream_t s) {
-  if (flat) return launch_variant_persistent<FastTracer<true, false>, true, false>(a, ticket, num_sms, s);
-  return launch_variant_persistent<FastTracer<false, false>, false, false>(a, ticket, num_sms, s);
+template <bool FLAT>
+static cudaError_t launch_fast_persistent(const FrameArgs& a, bool glass, unsigned int* ticket, int num_sms, cudaStream_t s) {
+  if (a.careful) return glass ? launch_variant_persistent<FastTracer<FLAT, false, true, true>, FLAT, false>(a, ticket, num_sms, s) : launch_variant_persistent<FastTracer<FLAT, false, true, false>, FLAT, false>(a, ticket, num_sms, s);
+  return glass ? launch_variant_persistent<FastTracer<FLAT, false, false, true>, FLAT, false>(a, ticket, num_sms, s) : launch_variant_persistent<FastTracer<FLAT, false, false, false>, FLAT, false>(a, ticket, num_sms, s);
+}
+
+cudaError_t launch_render_persistent(const FrameArgs& a, bool flat, bool glass, unsigned int* ticket, int num_sms, cudaStream_t s) {
+  return flat ? launch_fast_persistent<true>(a, glass, ticket, num_sms, s) : launch_fast_persistent<false>(a, glass, ticket, num_sms, s);
 }
 
 template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY>
@@ -160,10 +165,10 @@ static cudaError_t launch_variant(const FrameArgs& a, cudaStream_t s) {
 
 // Picks the instantiation of the timed (fast, no debug attachments) kernel: shading variant, CTA arrangement, and the two
 // specialisations that drop code a frame cannot reach (NOISE: rt_shade.cuh; GLASS: no voxel of material 2 in the chunk).
-template <bool FLAT, int WX, int WY>
-static cudaError_t launch_fast(const FrameArgs& a, bool noisy, bool glass, cudaStream_t s) {
-  if (noisy) return glass ? launch_variant<FastTracer<FLAT, false, true, true>, FLAT, false, WX, WY>(a, s) : launch_variant<FastTracer<FLAT, false, true, false>, FLAT, false, WX, WY>(a, s);
-  return glass ? launch_variant<FastTracer<FLAT, false, false, true>, FLAT, false, WX, WY>(a, s) : launch_variant<FastTracer<FLAT, false, false, false>, FLAT, false, WX, WY>(a, s);
+template <bool FLAT, bool DEBUG, int WX, int WY>
+static cudaError_t launch_fast(const FrameArgs& a, bool careful, bool glass, cudaStream_t s) {
+  if (careful) return glass ? launch_variant<FastTracer<FLAT, DEBUG, true, true>, FLAT, DEBUG, WX, WY>(a, s) : launch_variant<FastTracer<FLAT, DEBUG, true, false>, FLAT, DEBUG, WX, WY>(a, s);
+  return glass ? launch_variant<FastTracer<FLAT, DEBUG, false, true>, FLAT, DEBUG, WX, WY>(a, s) : launch_variant<FastTracer<FLAT, DEBUG, false, false>, FLAT, DEBUG, WX, WY>(a, s);
 }
 
 cudaError_t launch_render(const FrameArgs& a, bool exact, bool flat, bool debug, bool wide_rows, bool glass, cudaStream_t s) {
@@ -172,11 +177,13 @@ cudaError_t launch_render(const FrameArgs& a, bool exact, bool flat, bool debug,
     if (flat) return debug ? launch_variant<ExactTracer<true, true>, true, true, 2, 2>(a, s) : launch_variant<ExactTracer<true, false>, true, false, 2, 2>(a, s);
     return debug ? launch_variant<ExactTracer<false, true>, false, true, 2, 2>(a, s) : launch_variant<ExactTracer<false, false>, false, false, 2, 2>(a, s);
   }
-  if (debug) return flat ? launch_variant<FastTracer<true, true>, true, true, 2, 2>(a, s) : launch_variant<FastTracer<false, true>, false, true, 2, 2>(a, s);
-  // The reference's default is no noise at all (main.cpp:156-158): those frames run the instantiation that carries no hash code.
-  const bool noisy = a.p.rayNoise != 0.0f || a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f;
-  if (wide_rows) return flat ? launch_fast<true, 4, 1>(a, noisy, glass, s) : launch_fast<false, 4, 1>(a, noisy, glass, s);
-  return flat ? launch_fast<true, LX, LY>(a, noisy, glass, s) : launch_fast<false, LX, LY>(a, noisy, glass, s);
+  // The reference's default is no noise at all (main.cpp:156-158): those frames run the lean instantiation that carries no hash code;
+  // frames with a noise uniform set (or a camera on a far chunk face) run the careful one (rt_trace_fast.cuh).  The instrumented
+  // (debug) kernels are the same four instantiations with counters and attachments, so that what the tests look at is what is timed.
+  const bool careful = a.careful != 0;
+  if (debug) return flat ? launch_fast<true, true, 2, 2>(a, careful, glass, s) : launch_fast<false, true, 2, 2>(a, careful, glass, s);
+  if (wide_rows) return flat ? launch_fast<true, false, 4, 1>(a, careful, glass, s) : launch_fast<false, false, 4, 1>(a, careful, glass, s);
+  return flat ? launch_fast<true, false, LX, LY>(a, careful, glass, s) : launch_fast<false, false, LX, LY>(a, careful, glass, s);
 }
 
 }  // namespace vrt

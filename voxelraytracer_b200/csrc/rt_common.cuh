@@ -197,6 +197,9 @@ struct FrameArgs {
   int band_shift;           // log2(band_rows) when band_rows is a power of two (frame_row then needs no division), else -1
   int w_const;              // u_PVInvMatrix maps every pixel to the same clip w at the near and at the far plane (any perspective x rigid view)
   float inv_w_near, inv_w_far;   // then: 1 / that w (fast traversal's ray generation; see shade_pixel)
+  int careful;              // this frame runs the careful instantiation of the fast traversal (rt_trace_fast.cuh): some noise uniform is
+                            //   non-zero, or the near plane touches a far boundary plane of the chunk (see finish_frame_args)
+  int replay_glass;         // u_ReflectionNoise or u_RefractionNoise != 0: rays that end on glass are replayed with the pinned recurrence
   int ndc_by_rcp;           // (px + 0.5) / width and (py + 0.5) / height equal the reciprocal-multiply-correct form below for EVERY pixel
   float rcp_width, rcp_height;   //   of this frame size (checked exhaustively on the host): RN(1 / width), RN(1 / height)
 };
@@ -221,9 +224,11 @@ inline bool finish_frame_args(FrameArgs& a) {
   while ((1 << a.log2n) < a.p.size) a.log2n++;
   // Row 3 of the matrix is (0, 0, c, d) for the inverse of perspective x rigid view (src/main.cpp:69,75,161): the unprojected
   // w of a pixel does not depend on the pixel, so its reciprocal is a per-frame constant.  Same operations as shade_pixel.
-  a.w_const = a.p.invPV[3] == 0.0f && a.p.invPV[7] == 0.0f;
+  // A numerically inverted matrix may carry 1e-15 there instead of 0: still constant when |m3 nx + m7 ny| <= |m3| + |m7| stays below
+  // a quarter ulp of m11, because (xy -+ m11) then rounds to -+m11 for every pixel, exactly as with xy = 0.
+  a.w_const = a.p.invPV[11] != 0.0f && fabsf(a.p.invPV[3]) + fabsf(a.p.invPV[7]) <= 0.25f * (u2f(f2u(fabsf(a.p.invPV[11])) + 1u) - fabsf(a.p.invPV[11]));
   {
-    const float xy = a.p.invPV[3] * 0.0f + a.p.invPV[7] * 0.0f;
+    const float xy = 0.0f;
     a.inv_w_near = 1.0f / ((xy + a.p.invPV[11] * -1.0f) + a.p.invPV[15] * 1.0f);
     a.inv_w_far = 1.0f / ((xy + a.p.invPV[11] * 1.0f) + a.p.invPV[15] * 1.0f);
   }
@@ -239,6 +244,30 @@ inline bool finish_frame_args(FrameArgs& a) {
       cw = a.p.width; ch = a.p.height; cok = ok ? 1 : 0;
     }
     a.ndc_by_rcp = cok;
+  }
+  // Origins on a far boundary plane of the chunk (coordinate == size): GetVoxel lets them through its bounds test and the REPEAT
+  // wrap reads column 0 (voxel.glsl:151, main.cpp:315-318; pin G4) for as long as the float position stays ON the plane - a
+  // property of the pinned recurrence's roundings that only the literal replay reproduces.  If the near-plane rectangle (whose
+  // corners bound every pixel's origin; same arithmetic as shade_pixel) comes within 2^-19 size of such a plane, the frame runs the
+  // careful instantiation, which replays the rays that start there.  Ordinary cameras never do.
+  {
+    bool hazard = false;
+    const float* m = a.p.invPV;
+    float lo[3] = {finf(), finf(), finf()}, hi[3] = {-finf(), -finf(), -finf()};
+    for (int c = 0; c < 4; c++) {
+      const float nx = (c & 1) ? 1.0f : -1.0f, ny = (c & 2) ? 1.0f : -1.0f;
+      float nr[4];
+      for (int i = 0; i < 4; i++) nr[i] = ((m[i] * nx + m[4 + i] * ny) + m[8 + i] * -1.0f) + m[12 + i] * 1.0f;
+      for (int i = 0; i < 3; i++) {
+        const float q = nr[i] / nr[3] + a.fsize * 0.5f;
+        lo[i] = gmin(lo[i], q); hi[i] = gmax(hi[i], q);
+      }
+    }
+    const float eps = a.fsize * 1.9073486328125e-06f;
+    for (int i = 0; i < 3; i++) hazard = hazard || (lo[i] - eps <= a.fsize && hi[i] + eps >= a.fsize) || !(lo[i] == lo[i]) || !(hi[i] == hi[i]);
+    const bool noisy = a.p.rayNoise != 0.0f || a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f;
+    a.careful = (noisy || hazard) ? 1 : 0;
+    a.replay_glass = (a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f) ? 1 : 0;
   }
   a.band_shift = -1;
   if (a.p.band_count > 1 && a.p.band_rows > 0 && (a.p.band_rows & (a.p.band_rows - 1)) == 0)

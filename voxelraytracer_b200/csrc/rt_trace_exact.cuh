@@ -12,9 +12,10 @@
 
 namespace vrt {
 
-template <bool FLAT, bool COUNT>
+// GLASS only selects the context type (a chunk without material 2 can spawn no bounce ray, rt_shade.cuh); the two loops are the same.
+template <bool FLAT, bool COUNT, bool GLASS = true>
 struct ExactTracer {
-  typedef PixelCtx<FLAT, COUNT, false> Ctx;
+  typedef PixelCtx<FLAT, COUNT, false, true, GLASS> Ctx;
 
   // nextPlane (voxel.glsl:263-266, 306-309)
   static VRT_HD V3 first_planes(const V3& q, const V3& d) {

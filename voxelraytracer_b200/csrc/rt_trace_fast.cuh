@@ -25,8 +25,20 @@
 // place with the 10-bounce total-internal-reflection escape (voxel.glsl:357-380).
 // Float results differ from the shader's replayed recurrence only in the last ulps of the crossing
 // times, i.e. on rays grazing a voxel edge (north_star allows 0.01 % of the frame).
+//
+// Two kinds of instantiation (template flag NOISE, picked per frame by FrameArgs::careful, see finish_frame_args):
+//   NOISE = false  the lean one: every noise uniform is 0 (the reference's default, main.cpp:156-158), reciprocal-multiply arithmetic,
+//                  no hash code.  This is what the benchmarks time.
+//   NOISE = true   the careful one: ray construction with the pinned arithmetic of the shader (the hash behind the noise uniforms
+//                  turns a last-ulp difference of its inputs into a different random offset), and two replay rules that hand a ray
+//                  to the literal float recurrence (rt_trace_exact.cuh) where only its roundings give the reference's answer:
+//                   (1) u_ReflectionNoise / u_RefractionNoise != 0: a ray that ends on glass (or travels inside it) is replayed, so
+//                       that the hit point hashed into the bounce direction (voxel.glsl:132-140,203-246) has the reference's bits;
+//                       all other rays - the bulk - keep the skipping walk;
+//                   (2) a ray whose origin lies on a far boundary plane of the chunk (coordinate == size, pin G4).
 #pragma once
 #include "rt_shade.cuh"
+#include "rt_trace_exact.cuh"
 
 namespace vrt {
 
@@ -64,7 +76,14 @@ VRT_HD void keep_in_register(const uint16_t*&) {}
 
 template <bool FLAT, bool COUNT, bool NOISE = true, bool GLASS = true>
 struct FastTracer {
-  typedef PixelCtx<FLAT, COUNT, true, NOISE, GLASS> Ctx;
+  typedef PixelCtx<FLAT, COUNT, !NOISE, NOISE, GLASS> Ctx;
+  typedef ExactTracer<FLAT, COUNT, GLASS> Replay;          // same Ctx type when NOISE (the only case it is used in)
+
+  // replay rule (2): origin within 2^-20 size of a far boundary plane
+  static VRT_HD bool on_far_face(const V3& q, float s) {
+    const float e = s * 9.5367431640625e-07f;
+    return fabsf(q.x - s) <= e || fabsf(q.y - s) <= e || fabsf(q.z - s) <= e;
+  }
 
   // Position-dependent state of a walk; the direction constants are referenced, not copied, so that the
   // shadow rays read them straight from the kernel's constant bank.
@@ -271,7 +290,10 @@ struct FastTracer {
     }
   }
 
-  static VRT_HD bool shadow(Ctx& cx, const Ray& r, const Hit&) {
+  static VRT_HD bool shadow(Ctx& cx, const Ray& r, const Hit& hit) {
+    if constexpr (NOISE) {
+      if (on_far_face(r.pos, cx.f.fsize)) return Replay::shadow(cx, r, hit);
+    }
     cx.count(CNT_SHADOW);
     const int n = cx.f.p.size, P = cx.f.pitch;
     const DirConst& k = cx.f.sun;                          // shadow rays all point at the sun (voxel.glsl:191-201)
@@ -289,6 +311,18 @@ struct FastTracer {
   }
 
   static VRT_HD Hit march(Ctx& cx, Ray& r) {
+    if constexpr (NOISE) {
+      const bool glass_replay = GLASS && cx.f.replay_glass != 0;
+      if ((glass_replay && r.medium != 0) || on_far_face(r.pos, cx.f.fsize)) return Replay::march(cx, r);
+      Hit h = march_fast(cx, r);                             // a walk through air never rewrites the ray
+      if (glass_replay && h.found && h.voxel == 2) return Replay::march(cx, r);
+      return h;
+    } else {
+      return march_fast(cx, r);
+    }
+  }
+
+  static VRT_HD Hit march_fast(Ctx& cx, Ray& r) {
     Hit h;
     h.found = false;
     const int n = cx.f.p.size, P = cx.f.pitch;

@@ -304,7 +304,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   finish_frame_args(a);
   CU(cudaEventRecord(ctx->ev0, s));
   if ((p->flags & VRT_FLAG_PERSISTENT) && !debug && !(p->flags & (VRT_FLAG_EXACT | VRT_FLAG_RGB8_OUT))) {
-    CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, (unsigned int*)(ctx->d_stats + 4), ctx->num_sms, s));
+    CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, ctx->info.voxels_glass != 0, (unsigned int*)(ctx->d_stats + 4), ctx->num_sms, s));
   } else {
     CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, remote_target(ctx, d_out), ctx->info.voxels_glass != 0, s));
   }

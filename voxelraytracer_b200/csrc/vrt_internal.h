@@ -12,7 +12,7 @@ namespace vrt {
 // wide_rows: 32x4-pixel CTAs storing full 128-byte rows (for frames in another GPU's memory) instead of 16x8-pixel CTAs.
 cudaError_t launch_render(const FrameArgs& args, bool exact, bool flat, bool debug, bool wide_rows, bool glass, cudaStream_t stream);
 // Persistent variant of the fast kernel: one CTA per SM slot pulling 8x4-pixel warp tiles from an atomic queue.
-cudaError_t launch_render_persistent(const FrameArgs& args, bool flat, unsigned int* tile_counter, int num_sms, cudaStream_t stream);
+cudaError_t launch_render_persistent(const FrameArgs& args, bool flat, bool glass, unsigned int* tile_counter, int num_sms, cudaStream_t stream);
 
 // repack.cu: raw R8 grid (n^3) -> padded uint16 cells ((n+2)^3), see rt_trace_fast.cuh.
 // tmp_a / tmp_b: n^3 bytes of scratch each.  Returns the number of kernels launched through *launches.
