@@ -199,6 +199,8 @@ struct FrameArgs {
   float inv_w_near, inv_w_far;   // then: 1 / that w (fast traversal's ray generation; see shade_pixel)
   int careful;              // this frame runs the careful instantiation of the fast traversal (rt_trace_fast.cuh): some noise uniform is
                             //   non-zero, or the near plane touches a far boundary plane of the chunk (see finish_frame_args)
+  int replay_primary;       // the eye lies on a lattice line of the chunk (two coordinates integral): every primary ray runs along voxel
+                            //   edges again and again, exact ties that only the pinned recurrence's roundings decide -> primary rays are replayed
   int replay_glass;         // u_ReflectionNoise or u_RefractionNoise != 0: rays that end on glass are replayed with the pinned recurrence
   int ndc_by_rcp;           // (px + 0.5) / width and (py + 0.5) / height equal the reciprocal-multiply-correct form below for EVERY pixel
   float rcp_width, rcp_height;   //   of this frame size (checked exhaustively on the host): RN(1 / width), RN(1 / height)
@@ -265,8 +267,22 @@ inline bool finish_frame_args(FrameArgs& a) {
     }
     const float eps = a.fsize * 1.9073486328125e-06f;
     for (int i = 0; i < 3; i++) hazard = hazard || (lo[i] - eps <= a.fsize && hi[i] + eps >= a.fsize) || !(lo[i] == lo[i]) || !(hi[i] == hi[i]);
+    // Eye on a lattice line.  For a perspective matrix P (column 3 = (0,0,c,0)) the eye is the world point that P V maps to
+    // (0,0,c,0), i.e. column 2 of the inverse, dehomogenised.  With two of its chunk coordinates integral, pixel directions (rational
+    // multiples of each other on a regular pixel grid) meet voxel EDGES exactly, tie after tie; which cell the reference visits at a
+    // tie is decided by the last ulp of its re-derived plane times (voxel.glsl:323-331,381).  A measure-zero placement - the chunk
+    // centre (camera at the world origin) is the one a host is likely to pick - for which the primary rays take the literal replay.
+    a.replay_primary = 0;
+    if (m[11] != 0.0f) {
+      int integral = 0;
+      for (int i = 0; i < 3; i++) {
+        const float e = m[8 + i] / m[11] + a.fsize * 0.5f;
+        if (fabsf(e - rintf(e)) <= 6.103515625e-05f) integral++;
+      }
+      a.replay_primary = integral >= 2 ? 1 : 0;
+    }
     const bool noisy = a.p.rayNoise != 0.0f || a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f;
-    a.careful = (noisy || hazard) ? 1 : 0;
+    a.careful = (noisy || hazard || a.replay_primary) ? 1 : 0;
     a.replay_glass = (a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f) ? 1 : 0;
   }
   a.band_shift = -1;

@@ -35,7 +35,8 @@
 //                   (1) u_ReflectionNoise / u_RefractionNoise != 0: a ray that ends on glass (or travels inside it) is replayed, so
 //                       that the hit point hashed into the bounce direction (voxel.glsl:132-140,203-246) has the reference's bits;
 //                       all other rays - the bulk - keep the skipping walk;
-//                   (2) a ray whose origin lies on a far boundary plane of the chunk (coordinate == size, pin G4).
+//                   (2) a ray whose origin lies on a far boundary plane of the chunk (coordinate == size, pin G4);
+//                   (3) primary rays of a camera whose eye lies on a lattice line of the chunk (exact edge ties along every ray).
 #pragma once
 #include "rt_shade.cuh"
 #include "rt_trace_exact.cuh"
@@ -313,7 +314,8 @@ struct FastTracer {
   static VRT_HD Hit march(Ctx& cx, Ray& r) {
     if constexpr (NOISE) {
       const bool glass_replay = GLASS && cx.f.replay_glass != 0;
-      if ((glass_replay && r.medium != 0) || on_far_face(r.pos, cx.f.fsize)) return Replay::march(cx, r);
+      const bool primary = r.face_axis < 0;                  // every bounce ray starts on a voxel face
+      if ((glass_replay && r.medium != 0) || (primary && cx.f.replay_primary != 0) || on_far_face(r.pos, cx.f.fsize)) return Replay::march(cx, r);
       Hit h = march_fast(cx, r);                             // a walk through air never rewrites the ray
       if (glass_replay && h.found && h.voxel == 2) return Replay::march(cx, r);
       return h;
