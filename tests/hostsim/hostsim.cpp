@@ -185,6 +185,15 @@ int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cel
   return 0;
 }
 
+// 1 if finish_frame_args (the product's per-frame host logic) selects the careful instantiation for these params.
+int hostsim_frame_is_careful(const vrt_params* p) {
+  FrameArgs f;
+  std::memset(&f, 0, sizeof(f));
+  f.p = *p;
+  finish_frame_args(f);
+  return f.careful;
+}
+
 #ifdef VRT_HOST_HIST
 void hostsim_radius_hist(unsigned long long* out, int reset) {
   for (int i = 0; i < 256; i++) { out[i] = vrt::g_radius_hist[i]; if (reset) vrt::g_radius_hist[i] = 0; }

@@ -1,11 +1,13 @@
 """The product's device headers compiled for the host (tests/hostsim) against the oracle.
 Exact tracer: bit-identical.  Fast tracer: north_star's caps (hit map / bounce count differ on at most
 0.01 % of the frame; colour within 1/255 RMS per channel) - with a margin, at a size the CPU does in seconds."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
 import voxelraytracer_b200 as vrt
-from common import hostsim_cells, hostsim_render, make_params, oracle_render, rms255, scene
+from common import hostsim_cells, hostsim_lib, hostsim_render, make_params, oracle_render, rms255, scene
 
 CASES = [
     ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY),
@@ -120,7 +122,8 @@ def test_fast_tracer_with_noise_uniforms():
             assert (rms255(f.rgba8, o.rgba8) <= 1.0).all(), (sc, noise, rms255(f.rgba8, o.rgba8))
             ref_steps = o.counters["march_steps"] + o.counters["shadow_steps"]
             if sc == "terrain128_glass":
-                assert f.counters["actual_steps"] < 0.5 * ref_steps       # the replay is the exception, not the frame
+                # only glass-ending rays are replayed (this pose looks AT a glass wall), and none without bounce noise
+                assert f.counters["actual_steps"] < (0.7 if noise[1] or noise[2] else 0.5) * ref_steps
 
 
 def test_camera_on_a_far_chunk_face_replays_the_rays_that_start_on_it():
@@ -135,6 +138,22 @@ def test_camera_on_a_far_chunk_face_replays_the_rays_that_start_on_it():
     g = hostsim_render(p, grid, atlas, 1)
     assert int(((g.hit != o.hit) | (g.bounces != o.bounces)).sum()) == 0
     assert (rms255(g.rgba8, o.rgba8) <= 1.0).all()
+
+
+def test_lattice_line_eye_with_an_aligned_view_is_careful_and_generic_views_stay_lean():
+    """An eye on a lattice line whose view sends rays along voxel edges (axis-aligned, 45 degrees) ties on whole families of pixels:
+    finish_frame_args makes the frame careful and the tie-tracking walk replays the tied rays (fuzz seed 20261105 case 4: 52 px of
+    16 k before).  The same eye with a generic rotation - bench pose terrain_above sits on the line x = z = 64 - stays lean."""
+    for sc, pos, rot, W, H in (("terrain32", (-5.0, 1.0, -8.0), (0.0, -np.pi / 2, 0.0), 256, 64), ("terrain128_glass", (0.0, 0.0, 0.0), (0.0, np.pi / 4, 0.0), 320, 180)):
+        grid, n, atlas, ts = scene(sc)
+        p = make_params(W, H, sc, (pos, rot))
+        o = oracle_render(p, grid, atlas)
+        g = hostsim_render(p, grid, atlas, 1)
+        assert int(((g.hit != o.hit) | (g.bounces != o.bounces)).sum()) <= max(1, int(1e-4 * W * H)), (sc, rot)
+        assert (rms255(g.rgba8, o.rgba8) <= 1.0).all()
+    assert hostsim_lib().hostsim_frame_is_careful(C.byref(make_params(256, 64, "terrain32", ((-5.0, 1.0, -8.0), (0.0, -np.pi / 2, 0.0))))) == 1
+    for pose in ("terrain_inside", "terrain_low", "terrain_above", "terrain_outside", "start", "glass_wall", "refraction_close"):
+        assert hostsim_lib().hostsim_frame_is_careful(C.byref(make_params(1920, 1080, "terrain128", pose))) == 0, pose
 
 
 def test_randomised_poses_terminate_and_exact_replay_stays_bit_exact():

@@ -198,9 +198,8 @@ struct FrameArgs {
   int w_const;              // u_PVInvMatrix maps every pixel to the same clip w at the near and at the far plane (any perspective x rigid view)
   float inv_w_near, inv_w_far;   // then: 1 / that w (fast traversal's ray generation; see shade_pixel)
   int careful;              // this frame runs the careful instantiation of the fast traversal (rt_trace_fast.cuh): some noise uniform is
-                            //   non-zero, or the near plane touches a far boundary plane of the chunk (see finish_frame_args)
-  int replay_primary;       // the eye lies on a lattice line of the chunk (two coordinates integral): every primary ray runs along voxel
-                            //   edges again and again, exact ties that only the pinned recurrence's roundings decide -> primary rays are replayed
+                            //   non-zero, the near plane touches a far boundary plane of the chunk, or the eye sits on a lattice line
+                            //   with a view that sends rays along voxel edges (see finish_frame_args)
   int replay_glass;         // u_ReflectionNoise or u_RefractionNoise != 0: rays that end on glass are replayed with the pinned recurrence
   int ndc_by_rcp;           // (px + 0.5) / width and (py + 0.5) / height equal the reciprocal-multiply-correct form below for EVERY pixel
   float rcp_width, rcp_height;   //   of this frame size (checked exhaustively on the host): RN(1 / width), RN(1 / height)
@@ -268,21 +267,44 @@ inline bool finish_frame_args(FrameArgs& a) {
     const float eps = a.fsize * 1.9073486328125e-06f;
     for (int i = 0; i < 3; i++) hazard = hazard || (lo[i] - eps <= a.fsize && hi[i] + eps >= a.fsize) || !(lo[i] == lo[i]) || !(hi[i] == hi[i]);
     // Eye on a lattice line.  For a perspective matrix P (column 3 = (0,0,c,0)) the eye is the world point that P V maps to
-    // (0,0,c,0), i.e. column 2 of the inverse, dehomogenised.  With two of its chunk coordinates integral, pixel directions (rational
-    // multiples of each other on a regular pixel grid) meet voxel EDGES exactly, tie after tie; which cell the reference visits at a
-    // tie is decided by the last ulp of its re-derived plane times (voxel.glsl:323-331,381).  A measure-zero placement - the chunk
-    // centre (camera at the world origin) is the one a host is likely to pick - for which the primary rays take the literal replay.
-    a.replay_primary = 0;
+    // (0,0,c,0), i.e. column 2 of the inverse, dehomogenised.  With two of its chunk coordinates integral AND a view whose pixel
+    // directions stand in rational ratios (axis-aligned, 45 degrees ...), rays meet voxel EDGES exactly, tie after tie, and which
+    // cell the reference visits at a tie is decided by the last ulp of its re-derived plane times (voxel.glsl:323-331,381).  Probe:
+    // for 64 pixels spread over the frame, do the first 8 plane crossings of the two integral axes coincide anywhere?  A generic
+    // rotation gives none; two or more tying pixels make the frame careful (its tie-tracking walk then replays the tied rays).
+    bool lattice = false;
     if (m[11] != 0.0f) {
-      int integral = 0;
-      for (int i = 0; i < 3; i++) {
-        const float e = m[8 + i] / m[11] + a.fsize * 0.5f;
-        if (fabsf(e - rintf(e)) <= 6.103515625e-05f) integral++;
+      float e[3]; bool integral[3];
+      for (int i = 0; i < 3; i++) { e[i] = m[8 + i] / m[11] + a.fsize * 0.5f; integral[i] = fabsf(e[i] - rintf(e[i])) <= 6.103515625e-05f; }
+      if ((int)integral[0] + (int)integral[1] + (int)integral[2] >= 2) {
+        int tying = 0;
+        for (int sp = 0; sp < 64; sp++) {
+          const float px = (float)(((sp & 7) * 2 + 1) * a.p.width / 16), py = (float)(((sp >> 3) * 2 + 1) * a.p.height / 16);
+          const float nx = (px + 0.5f) / (float)a.p.width * 2.0f - 1.0f, ny = (py + 0.5f) / (float)a.p.height * 2.0f - 1.0f;
+          float nr[4], fr[4];
+          for (int i = 0; i < 4; i++) {
+            const float xy = m[i] * nx + m[4 + i] * ny;
+            nr[i] = (xy + m[8 + i] * -1.0f) + m[12 + i] * 1.0f; fr[i] = (xy + m[8 + i] * 1.0f) + m[12 + i] * 1.0f;
+          }
+          float d[3];
+          for (int i = 0; i < 3; i++) d[i] = fr[i] / fr[3] - nr[i] / nr[3];
+          bool tie = false;
+          for (int u = 0; u < 3 && !tie; u++)
+            for (int v = u + 1; v < 3 && !tie; v++) {
+              if (!integral[u] || !integral[v] || d[u] == 0.0f || d[v] == 0.0f) continue;
+              for (int i = 1; i <= 8 && !tie; i++)
+                for (int j = 1; j <= 8 && !tie; j++) {
+                  const float tu = (float)i / fabsf(d[u]), tv = (float)j / fabsf(d[v]);
+                  tie = fabsf(tu - tv) <= 2e-6f * tu;
+                }
+            }
+          tying += tie ? 1 : 0;
+        }
+        lattice = tying >= 2;
       }
-      a.replay_primary = integral >= 2 ? 1 : 0;
     }
     const bool noisy = a.p.rayNoise != 0.0f || a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f;
-    a.careful = (noisy || hazard || a.replay_primary) ? 1 : 0;
+    a.careful = (noisy || hazard || lattice) ? 1 : 0;
     a.replay_glass = (a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f) ? 1 : 0;
   }
   a.band_shift = -1;

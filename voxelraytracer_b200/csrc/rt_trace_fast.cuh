@@ -36,7 +36,11 @@
 //                       that the hit point hashed into the bounce direction (voxel.glsl:132-140,203-246) has the reference's bits;
 //                       all other rays - the bulk - keep the skipping walk;
 //                   (2) a ray whose origin lies on a far boundary plane of the chunk (coordinate == size, pin G4);
-//                   (3) primary rays of a camera whose eye lies on a lattice line of the chunk (exact edge ties along every ray).
+//                   (3) a ray whose walk STEPPED across two planes at (nearly) the same time - it passes through a voxel edge next to
+//                       an occupied cell, the one place where the last ulp of the reference's plane times decides which cell is
+//                       tested (the grazing rays of north_star).  Rare for a generic camera (~1e-4 of the rays); an eye on a
+//                       lattice line with an axis-aligned view ties on whole families of pixels, and finish_frame_args makes such
+//                       frames careful for that reason.
 #pragma once
 #include "rt_shade.cuh"
 #include "rt_trace_exact.cuh"
@@ -94,6 +98,8 @@ struct FastTracer {
     uint32_t idx;          // padded index of the current cell
     float t;               // entry time of the current cell
     int inc;               // index increment of the last step taken: +-1 (x plane), +-P (y), +-P*P (z)
+    float tol;             // careful instantiation: relative tie tolerance x (ray length so far + 1); a step whose two nearest
+    bool tie;              //   plane times differ by less than tol-scaled ulps sets `tie` (replay rule 3)
   };
   // Axis of the last plane crossed.  A cell with radius 0 is only ever entered by step() (a jump lands inside the
   // empty cube), so `inc` is always that of the crossing that produced a hit.
@@ -118,6 +124,11 @@ struct FastTracer {
     const bool sx = w.tmax.x == m;
     const bool sy = !sx && w.tmax.y == m;
     const bool sz = !sx && !sy;
+    if (NOISE) {
+      // second-nearest plane time; the pinned recurrence's times carry ~ulp(cumulative length) of error, the walk's ~ulp(t)
+      const float second = sx ? fminf(w.tmax.y, w.tmax.z) : (sy ? fminf(w.tmax.x, w.tmax.z) : fminf(w.tmax.x, w.tmax.y));
+      if (second - m <= (w.tol + m) * 1.0e-6f) w.tie = true;
+    }
     w.t = m;
     w.inc = sx ? k.dix : (sy ? k.diy : k.diz);
     w.idx += (uint32_t)w.inc;
@@ -189,6 +200,7 @@ struct FastTracer {
   static VRT_HD bool begin(Walk& w, const DirConst& k, const Ray& r, float fsize, int n, int P) {
     w.o = r.pos;
     w.inc = 0;
+    if (NOISE) w.tol = r.len + 1.0f;                       // `tie` is sticky over a march's restarts: cleared by the caller
     const float fn1 = (float)(n - 1);
     if (r.face_axis >= 0) {
       // Spawned on a voxel face: the start cell is the one on the parent ray's side of the face, taken from
@@ -291,40 +303,67 @@ struct FastTracer {
     }
   }
 
+  // replay rule (3) at the exit: the ray reaches a far boundary plane (coordinate == size) at the moment it crosses a lattice plane of
+  // another axis.  The reference samples that tie with the coordinate ON the plane, which passes GetVoxel's bounds test and wraps
+  // to column 0 (pin G4) - a hit where the walk sees the ray leave.
+  static VRT_HD bool leaves_through_far_edge(const Ray& r, float s) {
+    const float o[3] = {r.pos.x, r.pos.y, r.pos.z}, d[3] = {r.dir.x, r.dir.y, r.dir.z};
+    for (int a = 0; a < 3; a++) {
+      if (!(d[a] > 0.0f)) continue;
+      const float t = (s - o[a]) / d[a];
+      if (!(t > 0.0f)) continue;
+      const float tol = (r.len + t + 1.0f) * 2.0e-6f;
+      for (int b = 0; b < 3; b++) {
+        if (b == a) continue;
+        const float q = o[b] + t * d[b];
+        if (q >= -tol && q <= s + tol && fabsf(q - rintf(q)) <= tol) return true;
+      }
+    }
+    return false;
+  }
+
   static VRT_HD bool shadow(Ctx& cx, const Ray& r, const Hit& hit) {
     if constexpr (NOISE) {
       if (on_far_face(r.pos, cx.f.fsize)) return Replay::shadow(cx, r, hit);
     }
-    cx.count(CNT_SHADOW);
     const int n = cx.f.p.size, P = cx.f.pitch;
     const DirConst& k = cx.f.sun;                          // shadow rays all point at the sun (voxel.glsl:191-201)
     const uint16_t* cells = cx.f.sun_cells;                // the sun octant's radius field
     const float tcap = cx.f.p.maxRayLength - r.len;
     Walk w;
-    if (!begin(w, k, r, cx.f.fsize, n, P)) return false;
+    w.tie = false;
+    if (!begin(w, k, r, cx.f.fsize, n, P)) { cx.count(CNT_SHADOW); return false; }
     uint32_t rad = load_cell(cells, w.idx) >> 8;
+    bool result;
     for (;;) {
       const uint32_t c = walk_air(cx, w, k, cells, rad, tcap, P);
-      if (c == 0xFFFFFFFFu || c == 0u) return false;       // length cap / border: left the chunk
-      if (!Ctx::kGlass || !is_transparent((int)c)) return true;   // glass casts no shadow (voxel.glsl:288-295)
+      if (c == 0xFFFFFFFFu || c == 0u) { result = false; break; }       // length cap / border: left the chunk
+      if (!Ctx::kGlass || !is_transparent((int)c)) { result = true; break; }   // glass casts no shadow (voxel.glsl:288-295)
       rad = 0u;                                            // glass: one plain step onwards
     }
+    if constexpr (NOISE) {
+      if (w.tie || (!result && leaves_through_far_edge(r, cx.f.fsize))) return Replay::shadow(cx, r, hit);          // replay rule (3)
+    }
+    cx.count(CNT_SHADOW);
+    return result;
   }
 
   static VRT_HD Hit march(Ctx& cx, Ray& r) {
     if constexpr (NOISE) {
       const bool glass_replay = GLASS && cx.f.replay_glass != 0;
-      const bool primary = r.face_axis < 0;                  // every bounce ray starts on a voxel face
-      if ((glass_replay && r.medium != 0) || (primary && cx.f.replay_primary != 0) || on_far_face(r.pos, cx.f.fsize)) return Replay::march(cx, r);
-      Hit h = march_fast(cx, r);                             // a walk through air never rewrites the ray
-      if (glass_replay && h.found && h.voxel == 2) return Replay::march(cx, r);
+      if ((glass_replay && r.medium != 0) || on_far_face(r.pos, cx.f.fsize)) return Replay::march(cx, r);
+      Ray keep = r;
+      bool tied = false;
+      Hit h = march_fast(cx, r, tied);
+      if (tied || (glass_replay && h.found && h.voxel == 2) || (!h.found && leaves_through_far_edge(keep, cx.f.fsize))) { r = keep; return Replay::march(cx, r); }
       return h;
     } else {
-      return march_fast(cx, r);
+      bool tied = false;
+      return march_fast(cx, r, tied);
     }
   }
 
-  static VRT_HD Hit march_fast(Ctx& cx, Ray& r) {
+  static VRT_HD Hit march_fast(Ctx& cx, Ray& r, bool& tied) {
     Hit h;
     h.found = false;
     const int n = cx.f.p.size, P = cx.f.pitch;
@@ -336,7 +375,8 @@ struct FastTracer {
     keep_in_register(k.tdel.x); keep_in_register(k.tdel.y); keep_in_register(k.tdel.z);
     keep_in_register(k.off.x); keep_in_register(k.off.y); keep_in_register(k.off.z);
     Walk w;
-    if (!begin(w, k, r, cx.f.fsize, n, P)) return h;
+    w.tie = false;
+    if (!begin(w, k, r, cx.f.fsize, n, P)) { tied = w.tie; return h; }
     float tcap = cx.f.p.maxRayLength - r.len;
     int medium = Ctx::kGlass ? r.medium : 0;
     int tir = 0;
@@ -345,11 +385,11 @@ struct FastTracer {
       uint32_t c;
       if (!Ctx::kGlass || medium == 0) {
         c = walk_air(cx, w, k, cells, rad, tcap, P);
-        if (c == 0xFFFFFFFFu || c == 0u) return h;         // length cap / border while in air: left the chunk
+        if (c == 0xFFFFFFFFu || c == 0u) { tied = w.tie; return h; }         // length cap / border while in air: left the chunk
       } else {
         // inside a transparent medium (glass): plain steps until the voxel byte changes
         do {
-          if (!(w.t < tcap)) return h;
+          if (!(w.t < tcap)) { tied = w.tie; return h; }
           step(w, k);
           cx.count(CNT_ACTUAL_STEPS);
           c = load_cell(cells, w.idx);
@@ -366,6 +406,7 @@ struct FastTracer {
       if (is_hit) {
         h.cell = unpadded_index(w.idx, P, cx.f.log2n);
         h.found = true;
+        tied = w.tie;
         return h;
       }
       // leaving the transparent medium (voxel.glsl:357-380)
@@ -378,12 +419,12 @@ struct FastTracer {
         if (tir > 10) { r.dir = old_dir; r.medium = 0; }
       }
       medium = r.medium;
-      if (c == 0u && medium == 0) return h;                // refracted out through the chunk boundary
+      if (c == 0u && medium == 0) { tied = w.tie; return h; }                // refracted out through the chunk boundary
       // Restart the walk on the face just crossed.  The cell on the parent side is the medium cell the ray
       // was in; begin() derives it from face_nsign (the normal points back into that cell).
       set_dir_const(k, r.dir, P);
       cells = cx.f.cells + (size_t)k.oct * cx.f.oct_stride;
-      if (!begin(w, k, r, cx.f.fsize, n, P)) return h;
+      if (!begin(w, k, r, cx.f.fsize, n, P)) { tied = w.tie; return h; }
       tcap = cx.f.p.maxRayLength - r.len;
       rad = 0u;                                            // first move from the restart cell: one plain step
     }
