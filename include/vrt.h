@@ -39,8 +39,20 @@ enum {
 /* flags for vrt_params.flags */
 #define VRT_FLAG_COLOR_ONLY 0x1u /* the shader's `#define _COLOR_ONLY` variant (voxel.glsl:6,69-89,177-181,336-345) */
 #define VRT_FLAG_DEBUG_MAPS 0x2u /* also write the primary hit-voxel index map and the bounce-count map */
-#define VRT_FLAG_EXACT      0x4u /* literal float replay of the shader's DDA (bit-exact traversal); default is
-                                    the brick-skipping traversal, which may differ on grazing rays only */
+#define VRT_FLAG_EXACT      0x4u /* literal float replay of the shader's DDA for EVERY ray (bit-exact traversal, ~20x slower: a
+                                    verification mode).  The default is the empty-space-skipping traversal, which may differ on
+                                    grazing rays only (<= 0.01 % of the frame).  The default path selects per frame, by itself, a
+                                    "careful" kernel when the frame needs the reference's own roundings somewhere:
+                                      - a noise uniform is non-zero: rays are built with the shader's pinned arithmetic, and with
+                                        u_ReflectionNoise / u_RefractionNoise set every ray that ENDS ON GLASS is replayed with the
+                                        literal recurrence, so the hit point hashed into the bounce direction (voxel.glsl:132-140,
+                                        203-246) has the reference's bits; all other rays keep the skipping walk;
+                                      - the camera's near plane touches a far boundary plane of the chunk (coordinate == size, where
+                                        GetVoxel's `>` test and the REPEAT wrap read column 0): rays that start there are replayed;
+                                      - the eye lies on a lattice line of the chunk with a view that sends rays along voxel edges:
+                                        rays whose walk crossed two planes at (nearly) the same time are replayed.
+                                    Frames with all noise uniforms 0 and an ordinary camera - the reference's default and every
+                                    benchmark configuration - run the lean kernel. */
 #define VRT_FLAG_COUNTERS   0x8u /* accumulate ray/step counters (vrt_get_counters); slower, for tests/roofline */
 #define VRT_FLAG_FLOAT_OUT  0x10u /* also keep an unquantised float32 RGBA frame for RMS checks */
 #define VRT_FLAG_OUT_FRAME  0x20u /* vrt_render_to only: d_rgba8 is a FULL width x height frame and every pixel of the tile /
@@ -49,7 +61,8 @@ enum {
                                      NVLink with vrt_ipc_open): the gather is the kernel's own stores. */
 
 #define VRT_FLAG_PERSISTENT 0x40u /* tuning: persistent-warp launch (resident CTAs pull 8x4 patches from an atomic ticket)
-                                     instead of one CTA per 16x8 patch; same pixels.  Ignored with EXACT / debug flags. */
+                                     instead of one CTA per 16x8 patch; same pixels.  Ignored with EXACT / debug flags.  Each launch
+                                     has its own ticket word (ring of 16), so several may be in flight. */
 #define VRT_FLAG_RGB8_OUT   0x80u /* colour target is packed RGB8, 3 bytes per pixel, rows tight (the reference's colour attachment is
                                    * TextureInternalFormat::RGB, FrameBuffer.cpp:8,53; glReadPixels(GL_RGB) layout): 25 % fewer bytes
                                    * for a frame that leaves the GPU.  Every size below that says pixels*4 is pixels*3 then. */
@@ -103,6 +116,9 @@ int vrt_abi_version(void);
 int vrt_create(int device, vrt_ctx** out);
 int vrt_destroy(vrt_ctx* ctx);
 const char* vrt_last_error(const vrt_ctx* ctx); /* never NULL; ctx may be NULL (global last error) */
+/* Last non-fatal condition of this ctx ("" if none): e.g. vrt_upload_grid could not allocate the eight octant radius fields of a
+ * big chunk and built the single isotropic field instead (slower traversal, same pixels; vrt_grid_info.octants says 1). */
+const char* vrt_last_warning(const vrt_ctx* ctx);
 
 /* Replaces glTexImage3D(GL_TEXTURE_3D, GL_RED, size^3, GL_UNSIGNED_BYTE) (main.cpp:315-318).
  * voxels[x + y*size + z*size*size] (main.cpp:227); copied; size must be a power of two, 8..1024
@@ -145,8 +161,9 @@ int vrt_read_float_frame(vrt_ctx* ctx, float* rgba_f32, size_t npix);
 int vrt_reset_counters(vrt_ctx* ctx);
 int vrt_get_counters(vrt_ctx* ctx, vrt_counters* out);
 
-/* Device time of the last render's kernel(s) in milliseconds (CUDA events on the render stream);
- * replaces the GL_TIME_ELAPSED query at main.cpp:350-357.  Synchronises. */
+/* Device time of the most recent render CALL's kernel in milliseconds (CUDA events on its stream); replaces the
+ * GL_TIME_ELAPSED query at main.cpp:350-357.  Waits for that render.  Every call has its own event pair (a ring of 16), so
+ * up to 16 frames may be in flight on any number of streams without disturbing each other's timing. */
 int vrt_last_render_ms(vrt_ctx* ctx, float* ms);
 /* Number of kernels launched by this ctx since creation (for bench accounting). */
 int64_t vrt_kernel_launches(const vrt_ctx* ctx);
@@ -182,6 +199,10 @@ int vrt_host_alloc(vrt_ctx* ctx, size_t bytes, void** out);   /* pinned host mem
 int vrt_host_free(vrt_ctx* ctx, void* p);
 int vrt_device_alloc(vrt_ctx* ctx, size_t bytes, void** out);
 int vrt_device_free(vrt_ctx* ctx, void* p);
+/* cudaMemsetAsync on `stream`: FrameBuffer::Clear (FrameBuffer.cpp:37-40) without a host round trip. */
+int vrt_device_memset(vrt_ctx* ctx, void* d_ptr, int value, size_t bytes, void* stream);
+/* vrt_destroy releases whatever vrt_host_alloc / vrt_device_alloc / vrt_ipc_alloc_frame / vrt_ipc_open handed out and the
+ * caller did not give back. */
 int vrt_synchronize(vrt_ctx* ctx, void* stream);
 /* Measurement helper (no counterpart in the reference): read bandwidth in GB/s of a `bytes`-sized device buffer read
  * `passes` times by one kernel - 32 MiB stays in L2 (the denominator of the byte roofline), several GiB

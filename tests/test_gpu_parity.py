@@ -13,7 +13,7 @@ from common import gpu_render, hostsim_cells, hostsim_render, make_params, oracl
 pytestmark = pytest.mark.gpu
 
 CASES = [
-    ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY, 400, 400),     # C1 (main.cpp:438-439)
+    ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY, 400, 400),     # C1 frame size (main.cpp:438-439); the reference's aspect is tested below
     ("glass_cube32", "start", 0, 400, 400),
     ("terrain32", "terrain32_above", 0, 480, 270),
     ("terrain128", "terrain_inside", 0, 480, 270),
@@ -63,6 +63,154 @@ def test_fast_kernel_within_caps(ctx, sc, pose, flags, W, H):
     h = hostsim_render(p, grid, atlas, 1)
     assert np.array_equal(g.hit, h.hit) and np.array_equal(g.bounces, h.bounces)
     assert g.counters["actual_steps"] == h.counters["actual_steps"]
+
+
+def within_caps(g, o, W, H, what):
+    bad = int(((g.hit != o.hit) | (g.bounces != o.bounces)).sum())
+    assert bad <= max(2, int(1e-4 * W * H)), "%s: hit/bounce mismatches %d of %d" % (what, bad, W * H)
+    r = rms255(g.rgba8, o.rgba8)
+    assert (r <= 1.0).all(), (what, r)
+    return bad
+
+
+def test_c1_reference_aspect(ctx):
+    """BASELINE config 1 as the reference runs it: 400x400 frame but the projection keeps the WINDOW's aspect 1240/788
+    (main.cpp:436-439: _HIGH_PERFORMANCE resizes the buffers, not the camera), _COLOR_ONLY, 32^3 glass cube."""
+    grid, n, atlas, ts = upload(ctx, "glass_cube32")
+    p = make_params(400, 400, "glass_cube32", "start", vrt.FLAG_COLOR_ONLY, aspect=1240.0 / 788.0)
+    o = oracle_render(p, grid, atlas)
+    within_caps(gpu_render(ctx, p), o, 400, 400, "c1 fast")
+    pe = p.copy(); pe.flags |= vrt.FLAG_EXACT
+    e = gpu_render(ctx, pe)
+    assert np.array_equal(e.hit, o.hit) and np.array_equal(e.bounces, o.bounces)
+
+
+def test_c3_c4_full_size_against_the_oracle(ctx):
+    """BASELINE configs 3 and 4 at their full sizes, CUDA path vs the CPU oracle (not vs itself): 1920x1080 _REFRACTION and
+    3840x2160 terrain + glass walls, up to 9 marches per pixel."""
+    for sc, pose, W, H in (("refraction128", "refraction_close", 1920, 1080), ("terrain128_glass", "glass_wall", 3840, 2160),
+                           ("terrain128_glass", "terrain_inside", 3840, 2160)):
+        grid, n, atlas, ts = upload(ctx, sc)
+        p = make_params(W, H, sc, pose)
+        o = oracle_render(p, grid, atlas)
+        g = gpu_render(ctx, p)
+        within_caps(g, o, W, H, "%s/%s" % (sc, pose))
+        assert o.counters["secondary_rays"] > 0 and int(o.bounces.max()) >= 4
+        assert g.counters["primary_rays"] == W * H
+
+
+@pytest.mark.parametrize("sc,W,H,max_len,scale", [("synthetic512", 960, 540, 1024.0, 0.5), ("synthetic1024", 960, 540, 2048.0, 1.0)])
+def test_c5_big_chunks_against_the_oracle(ctx, sc, W, H, max_len, scale):
+    """BASELINE config 5's chunk (1024^3 procedural, maxRayLength 2048, orbit poses at radius 600) and its half-size rehearsal:
+    the radius-cap-96 branch of the repack, cell arrays beyond L2, jumps capped by the stored radius."""
+    import common
+    grid, n, atlas, ts = upload(ctx, sc)
+    info = ctx.grid_info()
+    assert info.radius_cap == 96 and info.octants == 8
+    for k in (0, 21):
+        p = make_params(W, H, sc, common.orbit_pose(k, 64, 600.0 * scale, 250.0 * scale), max_len=max_len)
+        o = oracle_render(p, grid, atlas)
+        g = gpu_render(ctx, p)
+        within_caps(g, o, W, H, "%s orbit%d" % (sc, k))
+        assert (o.hit != vrt.HIT_MISS).mean() > 0.2
+        assert g.counters["actual_steps"] * 10 < o.counters["march_steps"] + o.counters["shadow_steps"]
+    common._scene_cache.pop(sc, None)          # 1 GiB of host memory
+
+
+NOISE_CASES = [
+    ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY, 400, 400, (0.0, 0.1, 0.1)),
+    ("glass_cube32", "start", 0, 400, 400, (0.02, 0.1, 0.05)),
+    ("terrain128_glass", "glass_wall", 0, 960, 540, (0.0, 0.1, 0.1)),
+    ("terrain128_glass", "glass_wall", 0, 960, 540, (0.01, 0.05, 0.02)),
+    ("refraction128", "refraction_close", 0, 960, 540, (0.01, 0.05, 0.05)),
+    ("terrain128", "terrain_inside", 0, 960, 540, (0.02, 0.0, 0.0)),
+]
+
+
+@pytest.mark.parametrize("sc,pose,flags,W,H,noise", NOISE_CASES)
+def test_noise_uniforms_on_the_default_path(ctx, sc, pose, flags, W, H, noise):
+    """u_RayNoise / u_ReflectionNoise / u_RefractionNoise != 0 on the DEFAULT (fast) traversal: both bars of north_star against
+    the oracle.  Such frames run the careful instantiation - pinned ray construction, glass-ending rays replayed with the literal
+    recurrence so that the hashed hit point (voxel.glsl:132-140,203-246) has the reference's bits (rt_trace_fast.cuh)."""
+    grid, n, atlas, ts = upload(ctx, sc)
+    p = make_params(W, H, sc, pose, flags, noise=noise, time=3.0)
+    o = oracle_render(p, grid, atlas)
+    g = gpu_render(ctx, p)
+    within_caps(g, o, W, H, "%s %s" % (sc, noise))
+    h = hostsim_render(p, grid, atlas, 1)
+    assert np.array_equal(g.hit, h.hit) and np.array_equal(g.bounces, h.bounces)
+    assert np.array_equal(gpu_render(ctx, p, flags_extra=0).rgba8, g.rgba8)        # the timed kernel writes the same pixels
+
+
+def test_camera_on_far_face_and_lattice_eye(ctx):
+    """The two host-detected hazards (finish_frame_args): a camera exactly on the +x chunk face looking up, and an eye on a lattice
+    line with an axis-aligned view.  Both run the careful instantiation; device == host simulation, caps hold."""
+    for sc, pos, rot, W, H, kw in (("refraction32", (16.0, -7.1482414338108065, 15.1391967032303), (1.5692255304681018, -3.141592653589793, 0.0), 97, 61, dict(max_len=400.0)),
+                                   ("terrain32", (-5.0, 1.0, -8.0), (0.0, -np.pi / 2, 0.0), 256, 64, {}),
+                                   ("terrain128_glass", (0.0, 0.0, 0.0), (0.0, np.pi / 4, 0.0), 640, 360, {})):
+        grid, n, atlas, ts = upload(ctx, sc)
+        p = make_params(W, H, sc, (pos, rot), **kw)
+        o = oracle_render(p, grid, atlas)
+        g = gpu_render(ctx, p)
+        assert int(((g.hit != o.hit) | (g.bounces != o.bounces)).sum()) <= max(1, int(1e-4 * W * H)), sc
+        assert (rms255(g.rgba8, o.rgba8) <= 1.0).all()
+        h = hostsim_render(p, grid, atlas, 1)
+        assert np.array_equal(g.hit, h.hit) and np.array_equal(g.bounces, h.bounces)
+
+
+def _two_gpu_rank1(conn, sc, W, H, pose):
+    """Child process = rank 1 on cuda:1: maps rank 0's frame through CUDA IPC and stores its bands into it."""
+    try:
+        import voxelraytracer_b200 as v
+        from voxelraytracer_b200 import sharding
+        import common
+        grid, n, atlas, ts = common.scene(sc)
+        c = v.Context(1)
+        c.upload_grid(grid, n); c.upload_atlas(atlas, ts)
+        handle = conn.recv()
+        d = c.ipc_open(handle)
+        q = sharding.band_params(common.make_params(W, H, sc, pose), 1, 2, 16)
+        q.flags |= v.FLAG_OUT_FRAME
+        c.render_to(q, d, None); c.synchronize()
+        c.ipc_close(d)
+        c.close()
+        conn.send("ok")
+    except Exception as e:      # noqa: BLE001
+        conn.send("error: %r" % (e,))
+
+
+def test_two_gpus_render_bands_into_one_ipc_frame(ctx):
+    """N-GPU stitched frame == 1-GPU frame, byte for byte, through the product's own fused gather: rank 1 (another process on
+    cuda:1) stores its 16-row bands straight into rank 0's frame over NVLink (vrt_ipc_alloc_frame / vrt_ipc_open, VRT_FLAG_OUT_FRAME)."""
+    import multiprocessing as mp
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from voxelraytracer_b200 import sharding
+    sc, pose, W, H = "terrain128_glass", "glass_wall", 1920, 1080
+    grid, n, atlas, ts = upload(ctx, sc)
+    p = make_params(W, H, sc, pose)
+    full = gpu_render(ctx, p, flags_extra=0).rgba8.reshape(H, W, 4)
+    d, handle = ctx.ipc_alloc_frame(W * H * 4)
+    mpc = mp.get_context("spawn")
+    a, b = mpc.Pipe()
+    child = mpc.Process(target=_two_gpu_rank1, args=(b, sc, W, H, pose))
+    child.start()
+    try:
+        a.send(handle)
+        q = sharding.band_params(p, 0, 2, 16)
+        q.flags |= vrt.FLAG_OUT_FRAME
+        ctx.render_to(q, d, None); ctx.synchronize()
+        assert a.poll(300), "rank 1 did not answer"
+        msg = a.recv()
+        assert msg == "ok", msg
+        got = ctx.copy_to_host(d, W * H * 4).reshape(H, W, 4)
+        assert np.array_equal(got, full)
+    finally:
+        child.join(30)
+        if child.is_alive():
+            child.kill()
+        ctx.device_free(d)
 
 
 def test_plain_render_equals_debug_render(ctx):

@@ -23,7 +23,7 @@ SCENE_TERRAIN, SCENE_GLASS_CUBE, SCENE_REFRACTION, SCENE_SYNTHETIC = 0, 1, 2, 3
 
 # every symbol include/vrt.h declares (tests check that the library exports all of them)
 EXPORTS = [
-    "vrt_default_params", "vrt_abi_version", "vrt_create", "vrt_destroy", "vrt_last_error", "vrt_upload_grid",
+    "vrt_default_params", "vrt_abi_version", "vrt_create", "vrt_destroy", "vrt_last_error", "vrt_last_warning", "vrt_device_memset", "vrt_upload_grid",
     "vrt_upload_grid_device", "vrt_upload_atlas", "vrt_render", "vrt_render_to", "vrt_render_host", "vrt_tile_pixels", "vrt_probe_read_gbs",
     "vrt_framebuffer_device", "vrt_read_framebuffer", "vrt_read_debug_maps", "vrt_read_float_frame", "vrt_reset_counters",
     "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells", "vrt_set_option",
@@ -108,6 +108,8 @@ def _signatures():
         "vrt_create": (i32, [i32, C.POINTER(vp)]),
         "vrt_destroy": (i32, [vp]),
         "vrt_last_error": (C.c_char_p, [vp]),
+        "vrt_last_warning": (C.c_char_p, [vp]),
+        "vrt_device_memset": (i32, [vp, vp, i32, C.c_size_t, vp]),
         "vrt_upload_grid": (i32, [vp, vp, i32]),
         "vrt_upload_grid_device": (i32, [vp, vp, i32, vp]),
         "vrt_upload_atlas": (i32, [vp, vp, i32, i32]),
@@ -362,6 +364,12 @@ class Context:
         g = GridInfo()
         self._check(self.lib.vrt_grid_info_get(self.h, C.byref(g)))
         return g
+
+    def last_warning(self):
+        return self.lib.vrt_last_warning(self.h).decode()
+
+    def device_memset(self, d_ptr, value, nbytes, stream=None):
+        self._check(self.lib.vrt_device_memset(self.h, d_ptr, value, nbytes, stream))
 
     def set_option(self, option, value):
         self._check(self.lib.vrt_set_option(self.h, option, value))

@@ -10,6 +10,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "vrt_internal.h"
 
@@ -43,8 +44,16 @@ struct vrt_ctx {
   int64_t fb_pixels = 0;           // pixels of the last render INTO d_fb (vrt_render / pageable vrt_render_host)
   int fb_bpp = 4;                  // its bytes per pixel (3 with VRT_FLAG_RGB8_OUT)
   cudaStream_t last_stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  bool timed = false;
+  // Timing: a ring of event pairs, one per render call, so that frames in flight on several streams never share a pair;
+  // vrt_last_render_ms reads the pair of the most recent call.
+  static constexpr int kTimers = 16;
+  cudaEvent_t ev0[kTimers] = {nullptr}, ev1[kTimers] = {nullptr};
+  int timer_next = 0, timer_last = -1;
+  cudaEvent_t ev_fb = nullptr, ev_dbg = nullptr;   // completion of the last render into the ctx-owned frame / debug attachments
+  bool fb_pending = false, dbg_pending = false;
+  unsigned int* d_tickets = nullptr;               // persistent launches: one ticket word per launch, ring of kTimers
+  std::vector<void*> host_allocs, device_allocs, ipc_maps;   // handed out by vrt_host_alloc / vrt_device_alloc / vrt_ipc_*: released by vrt_destroy
+  std::string warn;                                // last non-fatal condition (vrt_last_warning)
   int64_t launches = 0;
   vrt_grid_info info{};
 };
@@ -82,9 +91,15 @@ static int ensure(vrt_ctx* ctx, T** p, size_t* have, size_t want) {
   return VRT_OK;
 }
 
+static void forget(std::vector<void*>& v, void* p) {
+  for (size_t i = 0; i < v.size(); i++)
+    if (v[i] == p) { v[i] = v.back(); v.pop_back(); return; }
+}
+
 extern "C" {
 
 const char* vrt_last_error(const vrt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_err.c_str(); }
+const char* vrt_last_warning(const vrt_ctx* ctx) { return ctx ? ctx->warn.c_str() : ""; }
 
 int vrt_create(int device, vrt_ctx** out) {
   vrt_ctx* ctx = nullptr;
@@ -104,8 +119,13 @@ int vrt_create(int device, vrt_ctx** out) {
   if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, device);
   if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->d_counters, sizeof(unsigned long long) * (CNT_N + 8));
   if (e == cudaSuccess) e = cudaMemset(ctx->d_counters, 0, sizeof(unsigned long long) * (CNT_N + 8));
-  if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
-  if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
+  for (int i = 0; i < vrt_ctx::kTimers && e == cudaSuccess; i++) {
+    e = cudaEventCreate(&ctx->ev0[i]);
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1[i]);
+  }
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_fb, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_dbg, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->d_tickets, sizeof(unsigned int) * vrt_ctx::kTimers);
   if (e != cudaSuccess) {
     int code = fail(nullptr, VRT_E_CUDA, "vrt_create: %s", cudaGetErrorString(e));
     delete ctx;
@@ -122,9 +142,18 @@ int vrt_destroy(vrt_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   cudaFree(ctx->d_grid); cudaFree(ctx->d_cells); cudaFree(ctx->d_atlas); cudaFree(ctx->d_fb); cudaFree(ctx->d_f32);
-  cudaFree(ctx->d_hit); cudaFree(ctx->d_bounces); cudaFree(ctx->d_counters);
-  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
-  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  cudaFree(ctx->d_hit); cudaFree(ctx->d_bounces); cudaFree(ctx->d_counters); cudaFree(ctx->d_tickets);
+  for (int i = 0; i < vrt_ctx::kTimers; i++) {
+    if (ctx->ev0[i]) cudaEventDestroy(ctx->ev0[i]);
+    if (ctx->ev1[i]) cudaEventDestroy(ctx->ev1[i]);
+  }
+  if (ctx->ev_fb) cudaEventDestroy(ctx->ev_fb);
+  if (ctx->ev_dbg) cudaEventDestroy(ctx->ev_dbg);
+  // whatever the caller did not give back: pinned host buffers, device buffers (IPC frames included), IPC mappings
+  for (void* p : ctx->ipc_maps) cudaIpcCloseMemHandle(p);
+  for (void* p : ctx->host_allocs) cudaFreeHost(p);
+  for (void* p : ctx->device_allocs) cudaFree(p);
+  cudaGetLastError();
   delete ctx;
   return VRT_OK;
 }
@@ -144,6 +173,10 @@ static int repack_locked(vrt_ctx* ctx, int size, cudaStream_t s) {
       if (ctx->d_cells) { cudaFree(ctx->d_cells); ctx->d_cells = nullptr; }
       tmp = nullptr;
       oct = 0;
+      char buf[256];
+      snprintf(buf, sizeof(buf), "vrt_upload_grid: %.1f GB for the eight octant radius fields of a %d^3 chunk could not be allocated; built the single "
+               "isotropic field instead (slower traversal, same pixels)", (double)(p3 * 16 + n3 * 3) / 1e9, size);
+      ctx->warn = buf;
     }
   }
   if (!oct) {
@@ -222,7 +255,7 @@ static int validate(vrt_ctx* ctx, const vrt_params* p) {
   if (!ctx->d_grid || !ctx->d_cells) return fail(ctx, VRT_E_NOT_READY, "render: no grid uploaded");
   if (p->size != ctx->size) return fail(ctx, VRT_E_INVALID, "render: params.size %d != uploaded grid size %d", p->size, ctx->size);
   if (p->width < 1 || p->height < 1 || p->width > 65536 || p->height > 65536) return fail(ctx, VRT_E_INVALID, "render: frame %dx%d", p->width, p->height);
-  if (p->tile_w < 1 || p->tile_h < 1 || p->tile_x0 < 0 || p->tile_y0 < 0 || p->tile_x0 + p->tile_w > p->width || p->tile_y0 + p->tile_h > p->height)
+  if (p->tile_w < 1 || p->tile_h < 1 || p->tile_x0 < 0 || p->tile_y0 < 0 || (int64_t)p->tile_x0 + p->tile_w > p->width || (int64_t)p->tile_y0 + p->tile_h > p->height)
     return fail(ctx, VRT_E_INVALID, "render: tile (%d,%d %dx%d) outside frame %dx%d", p->tile_x0, p->tile_y0, p->tile_w, p->tile_h, p->width, p->height);
   if (p->band_count > 1 && (p->band_rows < 1 || p->band_index < 0 || p->band_index >= p->band_count))
     return fail(ctx, VRT_E_INVALID, "render: band_rows %d band_count %d band_index %d", p->band_rows, p->band_count, p->band_index);
@@ -302,17 +335,20 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   if (p->flags & VRT_FLAG_COUNTERS) a.counters = ctx->d_counters;
   a.rows_local = (int)(npix / p->tile_w);
   finish_frame_args(a);
-  CU(cudaEventRecord(ctx->ev0, s));
+  const int tm = ctx->timer_next;
+  ctx->timer_next = (tm + 1) % vrt_ctx::kTimers;
+  CU(cudaEventRecord(ctx->ev0[tm], s));
   if ((p->flags & VRT_FLAG_PERSISTENT) && !debug && !(p->flags & (VRT_FLAG_EXACT | VRT_FLAG_RGB8_OUT))) {
-    CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, ctx->info.voxels_glass != 0, (unsigned int*)(ctx->d_stats + 4), ctx->num_sms, s));
+    CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, ctx->info.voxels_glass != 0, ctx->d_tickets + tm, ctx->num_sms, s));
   } else {
     CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, remote_target(ctx, d_out), ctx->info.voxels_glass != 0, s));
   }
-  CU(cudaEventRecord(ctx->ev1, s));
+  CU(cudaEventRecord(ctx->ev1[tm], s));
   ctx->launches += 1;
-  ctx->timed = true;
+  ctx->timer_last = tm;
   ctx->last_pixels = npix;
-  if (own_fb) { ctx->fb_pixels = npix; ctx->fb_bpp = (p->flags & VRT_FLAG_RGB8_OUT) ? 3 : 4; }
+  if (own_fb) { ctx->fb_pixels = npix; ctx->fb_bpp = (p->flags & VRT_FLAG_RGB8_OUT) ? 3 : 4; CU(cudaEventRecord(ctx->ev_fb, s)); ctx->fb_pending = true; }
+  if (debug) { CU(cudaEventRecord(ctx->ev_dbg, s)); ctx->dbg_pending = true; }
   ctx->last_stream = s;
   return VRT_OK;
 }
@@ -357,7 +393,7 @@ int vrt_read_framebuffer(vrt_ctx* ctx, uint8_t* host, size_t bytes) {
   if (bytes < (size_t)ctx->fb_pixels * ctx->fb_bpp) return fail(ctx, VRT_E_INVALID, "vrt_read_framebuffer: buffer %zu < %zu bytes", bytes, (size_t)ctx->fb_pixels * ctx->fb_bpp);
   int rc = bind(ctx);
   if (rc) return rc;
-  CU(cudaStreamSynchronize(ctx->last_stream));
+  if (ctx->fb_pending) CU(cudaEventSynchronize(ctx->ev_fb));     // the last render INTO d_fb, whatever stream it ran on
   CU(cudaMemcpy(host, ctx->d_fb, (size_t)ctx->fb_pixels * ctx->fb_bpp, cudaMemcpyDeviceToHost));
   return VRT_OK;
 }
@@ -367,7 +403,7 @@ int vrt_read_debug_maps(vrt_ctx* ctx, uint32_t* hit, uint8_t* bounces, size_t np
   if (!ctx->d_hit || !ctx->d_bounces || npix > (size_t)ctx->last_pixels) return fail(ctx, VRT_E_NOT_READY, "vrt_read_debug_maps: no debug maps for %zu pixels", npix);
   int rc = bind(ctx);
   if (rc) return rc;
-  CU(cudaStreamSynchronize(ctx->last_stream));
+  if (ctx->dbg_pending) CU(cudaEventSynchronize(ctx->ev_dbg));
   if (hit) CU(cudaMemcpy(hit, ctx->d_hit, npix * 4, cudaMemcpyDeviceToHost));
   if (bounces) CU(cudaMemcpy(bounces, ctx->d_bounces, npix, cudaMemcpyDeviceToHost));
   return VRT_OK;
@@ -378,7 +414,7 @@ int vrt_read_float_frame(vrt_ctx* ctx, float* rgba, size_t npix) {
   if (!ctx->d_f32 || npix > (size_t)ctx->last_pixels) return fail(ctx, VRT_E_NOT_READY, "vrt_read_float_frame: no float frame for %zu pixels", npix);
   int rc = bind(ctx);
   if (rc) return rc;
-  CU(cudaStreamSynchronize(ctx->last_stream));
+  if (ctx->dbg_pending) CU(cudaEventSynchronize(ctx->ev_dbg));
   CU(cudaMemcpy(rgba, ctx->d_f32, npix * 16, cudaMemcpyDeviceToHost));
   return VRT_OK;
 }
@@ -407,11 +443,11 @@ int vrt_get_counters(vrt_ctx* ctx, vrt_counters* out) {
 
 int vrt_last_render_ms(vrt_ctx* ctx, float* ms) {
   if (!ctx || !ms) return fail(ctx, VRT_E_INVALID, "vrt_last_render_ms: NULL argument");
-  if (!ctx->timed) return fail(ctx, VRT_E_NOT_READY, "vrt_last_render_ms: nothing rendered yet");
+  if (ctx->timer_last < 0) return fail(ctx, VRT_E_NOT_READY, "vrt_last_render_ms: nothing rendered yet");
   int rc = bind(ctx);
   if (rc) return rc;
-  CU(cudaEventSynchronize(ctx->ev1));
-  CU(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+  CU(cudaEventSynchronize(ctx->ev1[ctx->timer_last]));
+  CU(cudaEventElapsedTime(ms, ctx->ev0[ctx->timer_last], ctx->ev1[ctx->timer_last]));
   return VRT_OK;
 }
 
@@ -500,12 +536,16 @@ int vrt_host_alloc(vrt_ctx* ctx, size_t bytes, void** out) {
   int rc = bind(ctx);
   if (rc) return rc;
   CU(cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+  ctx->host_allocs.push_back(*out);
   return VRT_OK;
 }
 
 int vrt_host_free(vrt_ctx* ctx, void* p) {
   if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_host_free: NULL ctx");
-  if (p) CU(cudaFreeHost(p));
+  if (p) {
+    forget(ctx->host_allocs, p);
+    CU(cudaFreeHost(p));
+  }
   return VRT_OK;
 }
 
@@ -514,6 +554,15 @@ int vrt_device_alloc(vrt_ctx* ctx, size_t bytes, void** out) {
   int rc = bind(ctx);
   if (rc) return rc;
   CU(cudaMalloc(out, bytes));
+  ctx->device_allocs.push_back(*out);
+  return VRT_OK;
+}
+
+int vrt_device_memset(vrt_ctx* ctx, void* d_ptr, int value, size_t bytes, void* stream) {
+  if (!ctx || !d_ptr) return fail(ctx, VRT_E_INVALID, "vrt_device_memset: NULL argument");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaMemsetAsync(d_ptr, value, bytes, (cudaStream_t)stream));
   return VRT_OK;
 }
 
@@ -521,7 +570,10 @@ int vrt_device_free(vrt_ctx* ctx, void* p) {
   if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_device_free: NULL ctx");
   int rc = bind(ctx);
   if (rc) return rc;
-  if (p) CU(cudaFree(p));
+  if (p) {
+    forget(ctx->device_allocs, p);
+    CU(cudaFree(p));
+  }
   return VRT_OK;
 }
 
@@ -565,6 +617,7 @@ int vrt_ipc_alloc_frame(vrt_ctx* ctx, size_t bytes, void** d_ptr, uint8_t handle
   int rc = bind(ctx);
   if (rc) return rc;
   CU(cudaMalloc(d_ptr, bytes));
+  ctx->device_allocs.push_back(*d_ptr);
   cudaIpcMemHandle_t h;
   CU(cudaIpcGetMemHandle(&h, *d_ptr));
   memset(handle, 0, VRT_IPC_HANDLE_BYTES);
@@ -579,6 +632,7 @@ int vrt_ipc_open(vrt_ctx* ctx, const uint8_t handle[VRT_IPC_HANDLE_BYTES], void*
   cudaIpcMemHandle_t h;
   memcpy(&h, handle, sizeof(h));
   CU(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  ctx->ipc_maps.push_back(*d_ptr);
   if (ctx->ipc_n < 8) {
     uintptr_t base = (uintptr_t)*d_ptr;
     size_t n = mapped_range(*d_ptr, &base);
@@ -599,6 +653,7 @@ int vrt_ipc_close(vrt_ctx* ctx, void* d_ptr) {
         ctx->ipc_lo[i] = ctx->ipc_lo[ctx->ipc_n - 1]; ctx->ipc_hi[i] = ctx->ipc_hi[ctx->ipc_n - 1]; ctx->ipc_n--;
         break;
       }
+    forget(ctx->ipc_maps, d_ptr);
     CU(cudaIpcCloseMemHandle(d_ptr));
   }
   return VRT_OK;

@@ -63,7 +63,8 @@ class AppScene {
     vrt_params p;
     vrt_default_params(&p, (int)rayTraceFrameBuffer->GetWidth(), (int)rayTraceFrameBuffer->GetHeight(), (int)size);   // viewport, main.cpp:325
     rayTraceFrameBuffer->Enable();
-    rayTraceFrameBuffer->Clear();                                                     // main.cpp:326-327
+    // main.cpp:326-327 clears the target here; the tracer overwrites every pixel of it, so the clear is left out (FrameBuffer::Clear,
+    // a device memset, is still what Create / Resize run)
     for (int i = 0; i < 16; i++) p.invPV[i] = cam.GetInvPVMatrix()[i];                // u_PVInvMatrix, main.cpp:333
     p.atlasSize = 2 * texture_size_; p.atlasTextureSize = texture_size_;              // main.cpp:336-337
     p.rayNoise = rayNoise; p.reflectionNoise = reflectionNoise; p.refractionNoise = refractionNoise;   // main.cpp:340-342

@@ -66,9 +66,8 @@ class FrameBuffer {
   void Enable() { bound() = this; }                // the next AppScene draw renders into this target
   static void Disable() { bound() = nullptr; }
   static FrameBuffer* Bound() { return bound(); }
-  void Clear() {                                   // glClear of the colour attachment: opaque black
-    std::vector<uint32_t> z((size_t)width_ * height_, 0xFF000000u);
-    check(vrt_copy_to_device(dev_->ctx(), texture_, z.data(), bytes(), nullptr), dev_->ctx(), "FrameBuffer::Clear");
+  void Clear() {                                   // glClear of the colour attachment (default clear colour 0,0,0,0): a device memset
+    check(vrt_device_memset(dev_->ctx(), texture_, 0, bytes(), nullptr), dev_->ctx(), "FrameBuffer::Clear");
   }
   std::vector<uint8_t> Read() const {              // Utils::Screenshot's read-back (main.cpp:423-429)
     std::vector<uint8_t> out(bytes());
