@@ -61,68 +61,40 @@ WORKLOAD_DESC = {
     "c5s": "synthetic 512^3 procedural chunk, 3840x2160, 64 orbit poses, maxRayLength 1024 (half-size rehearsal of configs[4])",
 }
 I_STEP = 16          # algorithmic thread-instructions per reference DDA step
-# dram__bytes_read.sum + dram__bytes_write.sum per render_kernel launch from the committed `ncu --set full` capture (profiles/)
-NCU_TRAFFIC = {"c2": 2.9e6, "c5": 3.4e9}   # dram read + write per launch: profiles/r01_ncu_c2_end.txt, r01_ncu_c5.txt
-# smsp__issue_active (share of issue slots really used, i.e. the fraction of the issue roofline without the credit for skipped
-# steps) and executed thread-instructions per launch from the same captures; static numbers from profiles/, not measured by this run
-# (the C2 / C4 captures predate the kernel specialisations of profiles/r01_ab_specialisations.txt: traversal loop and data layout
-# are the same, the instruction count per pixel is lower now - to be re-captured with the next round's GPU budget)
-NCU_ISSUE = {"c2": (0.850, "profiles/r01_ncu_c2_end.txt (kernel build before the NOISE/GLASS specialisations)"),
-             "c4": (0.844, "profiles/r01_ncu_c4.txt (kernel build before the NOISE/GLASS specialisations)"), "c5": (0.777, "profiles/r01_ncu_c5.txt")}
+NCU_SUMMARY = os.path.join(ROOT, "profiles", "ncu_summary.json")
 
 
-def parse():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=300)
-    ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
-    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl", "none"],
-                    help="N>1: p2p = every rank's render kernel stores straight into rank 0's frame over NVLink (fused render+gather); "
-                         "nccl = all_gather_into_tensor after the render; none = frames stay on their GPUs")
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="weak: one full frame per GPU per step (pose batch); strong: ONE frame per step, 16-row bands dealt round-robin")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--octants", type=int, default=1, choices=[0, 1], help="VRT_OPT_OCTANT_FIELDS (tuning comparison; 1 = default)")
-    ap.add_argument("--radius-cap", type=int, default=0, help="VRT_OPT_RADIUS_CAP (tuning comparison; 0 = default)")
-    ap.add_argument("--no-affinity", action="store_true", help="N > 1: do not restrict each rank to its GPU's local host cores")
-    ap.add_argument("--e2e-depth", type=int, default=4, help="frames in flight in the overlapped e2e leg")
-    ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
-    return ap.parse_args()
+def ncu_entry(workload):
+    """Counters of the timed kernel from the committed `ncu --set full` capture of this workload (profiles/ncu_summary.json, written
+    by tools/ncu_summary.py from the .ncu-rep; per-launch means over the captured launches, one per cycled pose).  None if the
+    workload was never captured: nothing is typed into this file."""
+    try:
+        return json.load(open(NCU_SUMMARY)).get(workload)
+    except Exception:
+        return None
+
+
+def config_of(args, poses, W, H):
+    """The `config` object: the workload only, IDENTICAL in both arms (what differs between the arms is under `run`)."""
+    return {"workload": WORKLOAD_DESC[args.workload], "poses": poses if len(poses) <= 8 else "%d orbit poses" % len(poses), "frame": [W, H],
+            "maxRayLength": MAX_LEN.get(args.workload, 100.0),
+            "inputs": "reference texture tiles (tests/golden/ref_tiles.npz) for c1-c4, procedural atlas for c5; seeded value-noise heightmap",
+            "l2": "GPU arm: flushed by a 256 MiB fill before every timed step window (the fill itself is outside the window); CPU arm: n/a"}
 
 
 # ------------------------------------------------------------------ the reference arm (CPU)
-def strips(height, rows=12, every=4):
-    """Bounded sample of a frame: every `every`-th strip of `rows` scanlines."""
-    return [(y, min(rows, height - y)) for y in range(0, height, rows * every)]
+def row_blocks(height, rows):
+    """The frame as consecutive blocks of `rows` scanlines (the last one shorter)."""
+    return [(y, min(rows, height - y)) for y in range(0, height, rows)]
 
 
-def cpu_reference_frame(common, p, grid, atlas, sample, threads):
-    """Times the reference shader (oracle/_ref) - or the oracle port when _ref was never built - on `sample`
-    strips of the frame `p`.  Returns (seconds, kind)."""
-    use_ref = common.ref_lib() is not None
-    t0 = time.perf_counter()
-    for (y0, h) in sample:
-        q = p.copy()
-        q.tile_y0, q.tile_h = y0, h
-        if use_ref:
-            common.ref_render(q, grid, atlas, nthreads=threads)
-        else:
-            common.oracle_render(q, grid, atlas, nthreads=threads)
-    return time.perf_counter() - t0, ("reference" if use_ref else "port")
-
-
-def sample_rays(common, p, grid, atlas, sample, threads):
-    rays = steps = 0
-    for (y0, h) in sample:
-        q = p.copy()
-        q.tile_y0, q.tile_h = y0, h
-        c = common.oracle_render(q, grid, atlas, nthreads=threads).counters
-        rays += c["primary_rays"] + c["secondary_rays"] + c["shadow_rays"]
-        steps += c["march_steps"] + c["shadow_steps"]
-    return rays, steps
+def cpu_render(common, p, grid, atlas, threads, use_ref):
+    """One call into the reference shader (oracle/_ref, all `threads`; work items are 128-pixel row segments, so a block of a
+    few dozen rows keeps every thread busy) - or the oracle port when _ref was never built."""
+    if use_ref:
+        common.ref_render(p, grid, atlas, nthreads=threads)
+    else:
+        common.oracle_render(p, grid, atlas, nthreads=threads)
 
 
 def run_reference(args):
@@ -134,32 +106,59 @@ def run_reference(args):
     sc, poses, W, H, flags = WORKLOADS[args.workload]
     grid, n, atlas, ts = common.scene(sc)
     threads = os.cpu_count() or 1
+    use_ref = common.ref_lib() is not None
     frames = [mk(common, args.workload, W, H, sc, pose, flags) for pose in poses]
-    # Bounded sample: start from 1/4 of the scanlines and thin it until K + W steps fit in ~150 s on this box.
-    every = 4
-    dt, kind = cpu_reference_frame(common, frames[0], grid, atlas, strips(H, 12, every), threads)
+    # A step is a FULL frame when K + W of them fit in ~150 s on this box; otherwise a bounded sample: consecutive blocks of rows
+    # (at least 4 rows per thread), step i taking block i of pose i, so that the steps sweep every frame from bottom to top.
+    t0 = time.perf_counter()
+    cpu_render(common, frames[0], grid, atlas, threads, use_ref)
+    t_full = time.perf_counter() - t0
     budget = 150.0 / max(1, args.steps + args.warmup)
-    while dt > budget and every < H // 24:
-        every *= 2
-        dt /= 2.0
-    sample = strips(H, 12, every)
-    rays = [sample_rays(common, p, grid, atlas, sample, threads)[0] for p in frames]
+    rows = H
+    if t_full > budget:
+        rows = max(min(H, 4 * threads), int(H * budget / t_full))
+    blocks = row_blocks(H, rows)
+
+    def step_params(i):
+        q = frames[i % len(frames)].copy()
+        q.tile_y0, q.tile_h = blocks[i % len(blocks)]
+        return q
+
+    # rays of every distinct (pose, block) the timed steps touch, counted by the oracle outside the timing
+    ray_cache = {}
+
+    def rays_of(i):
+        key = (i % len(frames), i % len(blocks))
+        if key not in ray_cache:
+            c = common.oracle_render(step_params(i), grid, atlas, nthreads=threads).counters
+            ray_cache[key] = c["primary_rays"] + c["secondary_rays"] + c["shadow_rays"]
+        return ray_cache[key]
+
     for i in range(args.warmup):
-        cpu_reference_frame(common, frames[i % len(frames)], grid, atlas, sample, threads)
-    total_t = 0.0
+        cpu_render(common, step_params(i), grid, atlas, threads, use_ref)
+    times = []
     total_r = 0
     for i in range(args.steps):
-        dt, kind = cpu_reference_frame(common, frames[i % len(frames)], grid, atlas, sample, threads)
-        total_t += dt
-        total_r += rays[i % len(frames)]
+        q = step_params(i)
+        t0 = time.perf_counter()
+        cpu_render(common, q, grid, atlas, threads, use_ref)
+        times.append(time.perf_counter() - t0)
+    for i in range(args.steps):
+        total_r += rays_of(i)
+    total_t = sum(times)
     v = total_r / total_t / 1e6
+    kind = "reference" if use_ref else "port"
+    sample = ("full frames" if rows == H else "blocks of %d consecutive scanlines (1/%.1f of a frame per step), step i = block i of pose i" % (rows, H / rows)) + \
+             "; rays counted by the oracle on the same pixels"
     line = {
-        "impl": "reference", "metric": "Mrays/s at 1080p terrain scene", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / max(1, args.steps), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD_DESC[args.workload], "poses": poses, "frame": [W, H]},
-        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": kind,
-                         "sample": "every %dth 12-row strip of each frame (1/%d of the scanlines), rays counted on the same strips" % (every, every)},
+        "impl": "reference", "metric": "Mrays/s at 1080p terrain scene" if args.workload == "c2" else "Mrays/s", "value": v, "unit": "Mrays/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / max(1, args.steps),
+        "ms_per_step_median": 1e3 * float(np.median(times)), "ms_per_step_min": 1e3 * float(np.min(times)),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_of(args, poses, W, H),
+        "run": {"traversal": "the reference's voxel.glsl compiled as C++ (oracle/_ref)" if use_ref else "oracle port of voxel.glsl",
+                "sharding": "rank 0 only, %d host threads" % threads, "host_affinity": None},
+        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
@@ -441,7 +440,8 @@ def run_ours(args):
     t_wall = time.perf_counter() - t_wall0
     m1 = sampler.mark()
     launches_timed = ctx.kernel_launches() - launches0
-    t_steps = sum(a.elapsed_time(b) for a, b in ev) / 1e3
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    t_steps = sum(step_ms) / 1e3
 
     # kernel-only windows (for the roofline): the same steps without a gather inside the window
     if gather == "nccl":
@@ -621,31 +621,49 @@ def run_ours(args):
             + ", grid replicated; gather: " + {"p2p": "every rank's render kernel stores its pixels straight into rank 0's frame over NVLink (CUDA IPC mapping), "
                                                       "4-byte NCCL all-reduce per step as the completion signal (overlapped)",
                                                "nccl": "all_gather_into_tensor after the render, inside the step window", "none": "none"}[gather])
+        # What the timed kernel really executes, from the committed ncu capture of this workload at 1 GPU (per-launch means over the
+        # cycled poses); the TIME it is divided by is this run's own CUDA-event time.  Only meaningful when the launches are the
+        # captured ones: one GPU, full frames, default traversal.
+        nc = ncu_entry(args.workload) if (world == 1 and args.mode == "fast" and not args.persistent) else None
+        exec_per_launch = nc["thread_inst_per_launch"] if nc else None
+        ach_actual = exec_per_launch / per_launch_s if nc else None
+        traffic = nc["dram_bytes_per_launch"] if nc else None
+        roof = {"bound": "issue", "unit": "Tinstr/s", "peak": p_issue / 1e12,
+                "achieved": ach_actual / 1e12 if nc else None, "frac": ach_actual / p_issue if nc else None,
+                "frac_actual": ach_actual / p_issue if nc else None,
+                "achieved_def": "thread-instructions the kernel EXECUTES per launch (ncu smsp__inst_executed x lanes per instruction, mean over the cycled poses) "
+                                "/ this run's CUDA-event time per launch",
+                "peak_source": "%d SM x 4 schedulers x 32 lanes x sampled SM clock %.0f MHz" % (sms, f_mhz),
+                "traffic": traffic, "traffic_unit": "DRAM bytes read + written per launch (ncu --set full)",
+                "effective": {"achieved": ach_issue / 1e12, "frac": ach_issue / p_issue,
+                              "def": "SURVEY.md 8(d) algorithmic figure: %d thread-instr per REFERENCE DDA step x reference steps / time; empty-space skipping "
+                                     "executes far fewer steps than the reference takes, so this is a speed-up over the step floor, not a utilisation" % I_STEP},
+                "ncu": None if not nc else {k: nc[k] for k in ("file", "kernel", "commit", "launches", "duration_us_per_launch", "issue_active_pct",
+                                                                "lanes_per_inst", "warp_inst_per_launch", "thread_inst_per_pixel") if k in nc}}
+        dram_gbs = traffic / per_launch_s / 1e9 if nc else None
         line = {
             "metric": "Mrays/s at 1080p terrain scene" if args.workload == "c2" else "Mrays/s", "value": rays_all / t_step_total / 1e6,
             "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_step_total / args.steps,
+            "ms_per_step_median": float(np.median(step_ms)), "ms_per_step_min": float(np.min(step_ms)),
             "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_DESC[args.workload], "poses": poses if len(poses) <= 8 else "%d orbit poses" % len(poses), "frame": [W, H], "traversal": args.mode, "sharding": shard,
-                       "l2": "flushed: 256 MiB fill before every timed step window (the fill itself is outside the window)",
-                       "maxRayLength": MAX_LEN.get(args.workload, 100.0),
-                       "host_affinity": None if world == 1 else ("rank 0 on the %d host cores local to its GPU (NVML), likewise every rank" % host_cores
-                                                                 if host_cores else "not set")},
+            "config": config_of(args, poses, W, H),
+            "run": {"traversal": args.mode, "sharding": shard,
+                    "host_affinity": None if world == 1 else ("rank 0 on the %d host cores local to its GPU (NVML), likewise every rank" % host_cores
+                                                              if host_cores else "not set")},
             "frames_per_s": frames_total / t_step_total,
             "kernel_ms_per_launch": 1e3 * t_kernel_max / args.steps,
             "rays_per_frame": rays_all / frames_total, "ref_steps_per_frame": steps_all / frames_total,
             "actual_steps_per_frame": act_all / frames_total,
             "gsteps_per_s": steps_all / t_step_total / 1e9,
-            "roofline": {"bound": "issue", "achieved": ach_issue / 1e12, "peak": p_issue / 1e12, "unit": "Tinstr/s", "frac": ach_issue / p_issue,
-                         "traffic": NCU_TRAFFIC.get(args.workload), "traffic_unit": "DRAM bytes per launch (ncu --set full)",
-                         "peak_source": "%d SM x 4 schedulers x 32 lanes x sampled SM clock %.0f MHz" % (sms, f_mhz),
-                         "algorithmic": "%d thread-instr per reference DDA step x reference steps (SURVEY.md 8(d)); empty-space skipping executes "
-                                        "fewer steps than the reference takes, hence frac > 1 is possible" % I_STEP,
-                         "issue_slots_busy_ncu": NCU_ISSUE.get(args.workload, (None, None))[0], "issue_slots_busy_source": NCU_ISSUE.get(args.workload, (None, None))[1]},
-            "roofline_hbm": {"bound": "hbm", "achieved": bytes_per_launch / per_launch_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": bytes_per_launch / per_launch_s / 1e9 / hbm_peak, "traffic": NCU_TRAFFIC.get(args.workload),
+            "roofline": roof,
+            "roofline_hbm": {"bound": "hbm", "achieved": dram_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": dram_gbs / hbm_peak if nc else None,
+                             "achieved_def": "measured DRAM traffic per launch (ncu) / this run's time per launch: HBM is not the bound of this path",
+                             "algorithmic_gbs": bytes_per_launch / per_launch_s / 1e9,
+                             "algorithmic_def": "1 B per reference DDA step + 4 B per shaded hit + 4 B per pixel (SURVEY.md 8(d)); mostly bytes the skipping walk never touches",
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"},
             "roofline_l2": {"bound": "l2", "achieved": bytes_per_launch / per_launch_s / 1e9, "peak": l2_gbs, "unit": "GB/s",
                             "frac": bytes_per_launch / per_launch_s / 1e9 / l2_gbs if l2_gbs else None,
+                            "achieved_def": "algorithmic bytes (see roofline_hbm.algorithmic_def) / time",
                             "peak_source": "vrt_probe_read_gbs: 32 MiB buffer read 400 times by one kernel on this GPU, just now",
                             "hbm_probe_gbs": hbm_probe_gbs, "hbm_probe": "same kernel, 4 GiB buffer, 4 passes"},
             "e2e": {"value": rays_all / t_e2e / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(vrt.Params), "d2h_bytes_per_step": my_pix * 4,

@@ -63,13 +63,13 @@ static void set_uniforms(const vrt_params* p, const uint8_t* grid, const uint8_t
 #undef SET_FRAG
 }
 
-static void render_rows(const vrt_params* p, int row_begin, int row_end, float* out_rgba, uint32_t* out_fetch3d,
+static void render_rows(const vrt_params* p, int row_begin, int row_end, int col_begin, int col_end, float* out_rgba, uint32_t* out_fetch3d,
                         uint32_t* out_fetch2d) {
   const bool color_only = (p->flags & VRT_FLAG_COLOR_ONLY) != 0;
   const float W = (float)p->width, H = (float)p->height;
   for (int ly = row_begin; ly < row_end; ly++) {
     int y = p->tile_y0 + ly;
-    for (int lx = 0; lx < p->tile_w; lx++) {
+    for (int lx = col_begin; lx < col_end; lx++) {
       int x = p->tile_x0 + lx;
       // pixel centre in NDC; same float expression in the oracle and in the CUDA kernels
       float nx = ((float)x + 0.5f) / W * 2.0f - 1.0f;
@@ -117,14 +117,15 @@ int vref_render(const vrt_params* p, const uint8_t* grid, const uint8_t* atlas, 
   if (!(p->flags & VRT_FLAG_COLOR_ONLY) && !atlas) return -1;
   set_uniforms(p, grid, atlas);
   if (nthreads < 1) nthreads = 1;
+  // work item = one 128-pixel segment of one row: a strip of a few rows still keeps every thread busy
   std::atomic<int> next(0);
-  const int chunk = 1;
+  const int seg = 128, segs = (p->tile_w + seg - 1) / seg, items = segs * p->tile_h;
   auto work = [&]() {
     for (;;) {
-      int r0 = next.fetch_add(chunk);
-      if (r0 >= p->tile_h) break;
-      int r1 = r0 + chunk < p->tile_h ? r0 + chunk : p->tile_h;
-      render_rows(p, r0, r1, out_rgba, out_fetch3d, out_fetch2d);
+      int it = next.fetch_add(1);
+      if (it >= items) break;
+      int row = it / segs, c0 = (it % segs) * seg;
+      render_rows(p, row, row + 1, c0, c0 + seg < p->tile_w ? c0 + seg : p->tile_w, out_rgba, out_fetch3d, out_fetch2d);
     }
   };
   std::vector<std::thread> th;
