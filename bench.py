@@ -82,6 +82,28 @@ def config_of(args, poses, W, H):
             "l2": "GPU arm: flushed by a 256 MiB fill before every timed step window (the fill itself is outside the window); CPU arm: n/a"}
 
 
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl", "none"],
+                    help="N>1: p2p = every rank's render kernel stores straight into rank 0's frame over NVLink (fused render+gather); "
+                         "nccl = all_gather_into_tensor after the render; none = frames stay on their GPUs")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: one full frame per GPU per step (pose batch); strong: ONE frame per step, 16-row bands dealt round-robin")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--octants", type=int, default=1, choices=[0, 1], help="VRT_OPT_OCTANT_FIELDS (tuning comparison; 1 = default)")
+    ap.add_argument("--radius-cap", type=int, default=0, help="VRT_OPT_RADIUS_CAP (tuning comparison; 0 = default)")
+    ap.add_argument("--no-affinity", action="store_true", help="N > 1: do not restrict each rank to its GPU's local host cores")
+    ap.add_argument("--e2e-depth", type=int, default=4, help="frames in flight in the overlapped e2e leg")
+    ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
+    return ap.parse_args()
+
+
 # ------------------------------------------------------------------ the reference arm (CPU)
 def row_blocks(height, rows):
     """The frame as consecutive blocks of `rows` scanlines (the last one shorter)."""
