@@ -67,6 +67,12 @@ enum {
                                    * TextureInternalFormat::RGB, FrameBuffer.cpp:8,53; glReadPixels(GL_RGB) layout): 25 % fewer bytes
                                    * for a frame that leaves the GPU.  Every size below that says pixels*4 is pixels*3 then. */
 
+#define VRT_FLAG_CAREFUL    0x100u /* run the careful kernel (see VRT_FLAG_EXACT above) for this frame whatever the uniforms: rays that
+                                    * graze a voxel edge next to an occupied cell are replayed with the literal recurrence.  For frames
+                                    * whose hit map must follow the reference's own float drift: with u_MaxRayLength in the thousands
+                                    * (1024^3 chunks) the shader's `rayLength += tMin` accumulates ~1e-3 cells of error, and the skipping
+                                    * walk - which does not accumulate - disagrees with it on ~0.03 % of the pixels instead of < 0.01 %. */
+
 #define VRT_HIT_MISS 0xFFFFFFFFu
 
 /* Per-frame inputs == the uniforms AppScene::Render() sets (src/main.cpp:333-348; declared at

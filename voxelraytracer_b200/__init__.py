@@ -9,6 +9,7 @@ importing ``load_library`` raises ``ImportError`` when ``libvrt.so`` has not bee
 (``python -c "import __graft_entry__ as g; g.build()"`` or ``make -C voxelraytracer_b200/csrc``).
 """
 from .api import (  # noqa: F401
+    FLAG_CAREFUL,
     FLAG_COLOR_ONLY,
     FLAG_COUNTERS,
     FLAG_DEBUG_MAPS,
