@@ -165,7 +165,7 @@ def load_host_library():
     global _host_lib
     if _host_lib is not None:
         return _host_lib
-    path = os.path.join(os.path.dirname(lib_path()), "libvrt_host.so")
+    path = os.path.join(_HERE, "libvrt_host.so")          # always the in-tree one (VRT_LIBRARY only swaps the device library)
     if not os.path.exists(path):
         raise ImportError("libvrt_host.so is not built (%s missing); run `make -C voxelraytracer_b200/csrc`" % path)
     lib = C.CDLL(path)
