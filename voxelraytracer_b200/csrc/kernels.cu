@@ -84,6 +84,13 @@ __global__ void __launch_bounds__(WX * WY * 32, min_ctas(WX * WY)) render_kernel
   // memory and each thread stores the pixel at (tid % CW, tid / CW), so that a warp writes whole row segments.
   __shared__ uchar4 patch[CH][CW];
   uchar4 q = make_uchar4(0, 0, 0, 255);
+  // Frames in this GPU's own memory (the 2x2 arrangement) as RGBA8: every thread stores its own pixel - a warp's 8x4 patch is four
+  // 32-byte row pieces, i.e. four fully used DRAM sectors per store instruction - with no shared-memory stage and no CTA barrier
+  // (a warp that is done retires instead of waiting for the slowest of the four).
+  if (WX == 2 && !(f.p.flags & VRT_FLAG_RGB8_OUT)) {
+    render_one<Tracer, FLAT, DEBUG, false>(f, lx, ly);
+    return;
+  }
   render_one<Tracer, FLAT, DEBUG, true>(f, lx, ly, &q);
   patch[ly - by * CH][lx - blockIdx.x * CW] = q;
   __syncthreads();

@@ -128,6 +128,29 @@ struct Ray {
   float face_nsign;
 };
 
+// A bounce ray waiting on the per-pixel stack: what is read back, packed into 36 bytes (three vector accesses of local memory
+// instead of thirteen scalar ones).  medium is a voxel byte; the depths fit 8 bits (maxReflections + maxTransparencies <= 7, and the
+// transparency depth never drops below 0); face_axis is 0..2 for every bounce ray, face_nsign is +-1.
+struct alignas(16) PackedRay {
+  float px, py, pz, dx;
+  float dy, dz, len, energy;
+  uint32_t bits;
+};
+VRT_HD PackedRay pack_ray(const Ray& r) {
+  PackedRay q;
+  q.px = r.pos.x; q.py = r.pos.y; q.pz = r.pos.z; q.dx = r.dir.x; q.dy = r.dir.y; q.dz = r.dir.z; q.len = r.len; q.energy = r.energy;
+  q.bits = (uint32_t)(r.medium & 0xFF) | ((uint32_t)(r.nrefl & 0xFF) << 8) | ((uint32_t)(r.ntrans & 0xFF) << 16) | ((uint32_t)(r.face_axis & 3) << 24) |
+           (r.face_nsign > 0.0f ? 0x4000000u : 0u);
+  return q;
+}
+VRT_HD Ray unpack_ray(const PackedRay& q) {
+  Ray r;
+  r.pos = mk3(q.px, q.py, q.pz); r.dir = mk3(q.dx, q.dy, q.dz); r.len = q.len; r.energy = q.energy;
+  r.medium = (int)(q.bits & 0xFFu); r.nrefl = (int)((q.bits >> 8) & 0xFFu); r.ntrans = (int)(int8_t)((q.bits >> 16) & 0xFFu);
+  r.face_axis = (int)((q.bits >> 24) & 3u); r.face_nsign = (q.bits & 0x4000000u) ? 1.0f : -1.0f;
+  return r;
+}
+
 struct Hit {
   bool found;
   int voxel;           // byte
@@ -304,7 +327,7 @@ inline bool finish_frame_args(FrameArgs& a) {
       }
     }
     const bool noisy = a.p.rayNoise != 0.0f || a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f;
-    a.careful = (noisy || hazard || lattice || (a.p.flags & VRT_FLAG_CAREFUL)) ? 1 : 0;
+    a.careful = (noisy || hazard || lattice) ? 1 : 0;
     a.replay_glass = (a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f) ? 1 : 0;
   }
   a.band_shift = -1;

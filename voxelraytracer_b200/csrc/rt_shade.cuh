@@ -240,7 +240,7 @@ VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
     vdir = mk3(fr[0] / fr[3] - vnear.x, fr[1] / fr[3] - vnear.y, fr[2] / fr[3] - vnear.z);
   }
   constexpr int kStack = 8;  // maxReflections + maxTransparencies + 1 <= 8 (checked by the API)
-  Ray stack[kStack];         // only bounce rays ever live here; the primary ray stays in registers
+  PackedRay stack[kStack];   // only bounce rays ever live here (packed, rt_common.cuh); the primary ray stays in registers
   float half = cx.f.fsize * 0.5f;
   Ray r;
   r.pos = mk3(vnear.x + half, vnear.y + half, vnear.z + half);
@@ -258,15 +258,15 @@ VRT_HD PixelResult shade_pixel(typename Tracer::Ctx& cx, int px, int py) {
     popped++;
     if (Tracer::Ctx::kGlass && h.found) {
       MatProps mt = material_of<FLAT>(h.voxel);
-      if (mt.reflective && r.nrefl < p.maxReflections && n < kStack) stack[n++] = cx.reflection_of(r, h);
+      if (mt.reflective && r.nrefl < p.maxReflections && n < kStack) stack[n++] = pack_ray(cx.reflection_of(r, h));
       if (mt.transparent && r.ntrans < p.maxTransparencies) {
         float c[4];
         cx.color_of(h, c);
-        if (c[3] != 1.0f && n < kStack) stack[n++] = cx.refraction_of(r, h);
+        if (c[3] != 1.0f && n < kStack) stack[n++] = pack_ray(cx.refraction_of(r, h));
       }
     }
     if (!Tracer::Ctx::kGlass || n == 0) break;
-    r = stack[--n];
+    r = unpack_ray(stack[--n]);
   }
   out.rgba[0] = color.x; out.rgba[1] = color.y; out.rgba[2] = color.z; out.rgba[3] = 1.0f;
   out.bounces = popped;

@@ -127,10 +127,7 @@ struct FastTracer {
     if (NOISE) {
       // second-nearest plane time; the pinned recurrence's times carry ~ulp(cumulative length) of error, the walk's ~ulp(t)
       const float second = sx ? fminf(w.tmax.y, w.tmax.z) : (sy ? fminf(w.tmax.x, w.tmax.z) : fminf(w.tmax.x, w.tmax.y));
-      // the recurrence adds one rounding of the CUMULATIVE length per step, so its drift grows like sqrt(steps) x ulp(length):
-      // ~1e-4 cells after 100 units, ~3e-3 after 1000 (1024^3 chunks with u_MaxRayLength 2048)
-      const float T = w.tol + m;
-      if (second - m <= T * (1.0e-6f + 1.0e-7f * sqrtf(T))) w.tie = true;
+      if (second - m <= (w.tol + m) * 1.0e-6f) w.tie = true;
     }
     w.t = m;
     w.inc = sx ? k.dix : (sy ? k.diy : k.diz);
