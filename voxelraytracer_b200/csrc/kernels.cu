@@ -73,7 +73,10 @@ __device__ __forceinline__ void render_one(const FrameArgs& f, int lx, int ly, u
 #endif
 // resident warps per SM stay at VRT_MIN_BLOCKS x 4 whatever the CTA size (at most 32 CTAs fit on an SM)
 constexpr int min_ctas(int warps) { return VRT_MIN_BLOCKS * 4 / warps > 32 ? 32 : (VRT_MIN_BLOCKS * 4 / warps > 0 ? VRT_MIN_BLOCKS * 4 / warps : 1); }
-template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY>
+// DIRECT: every thread stores its own pixel (frames in this GPU's own memory as RGBA8: a warp's 8x4 patch is four 32-byte row pieces,
+// i.e. four fully used DRAM sectors per store instruction) - no shared-memory stage, no CTA barrier, a warp that is done retires
+// instead of waiting for the slowest of the four (C2 0.0665 -> 0.0642 ms, profiles/r02_ab_direct_store_packed_stack.txt).
+template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY, bool DIRECT>
 __global__ void __launch_bounds__(WX * WY * 32, min_ctas(WX * WY)) render_kernel(const __grid_constant__ FrameArgs f) {
   constexpr int CW = kWarpW * WX, CH = kWarpH * WY;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -84,10 +87,7 @@ __global__ void __launch_bounds__(WX * WY * 32, min_ctas(WX * WY)) render_kernel
   // memory and each thread stores the pixel at (tid % CW, tid / CW), so that a warp writes whole row segments.
   __shared__ uchar4 patch[CH][CW];
   uchar4 q = make_uchar4(0, 0, 0, 255);
-  // Frames in this GPU's own memory (the 2x2 arrangement) as RGBA8: every thread stores its own pixel - a warp's 8x4 patch is four
-  // 32-byte row pieces, i.e. four fully used DRAM sectors per store instruction - with no shared-memory stage and no CTA barrier
-  // (a warp that is done retires instead of waiting for the slowest of the four).
-  if (WX == 2 && !(f.p.flags & VRT_FLAG_RGB8_OUT)) {
+  if (DIRECT) {
     render_one<Tracer, FLAT, DEBUG, false>(f, lx, ly);
     return;
   }
@@ -166,7 +166,9 @@ static cudaError_t launch_variant(const FrameArgs& a, cudaStream_t s) {
   constexpr int CW = kWarpW * WX, CH = kWarpH * WY;
   dim3 grid((unsigned)((a.p.tile_w + CW - 1) / CW), (unsigned)((a.rows_local + CH - 1) / CH));
   if (grid.x == 0 || grid.y == 0) return cudaSuccess;
-  render_kernel<Tracer, FLAT, DEBUG, WX, WY><<<grid, WX * WY * 32, 0, s>>>(a);
+  // packed RGB8 rows and remote targets (4 x 1 arrangement, full 128-byte rows) go through the shared-memory transpose
+  if (WX == 2 && !(a.p.flags & VRT_FLAG_RGB8_OUT)) render_kernel<Tracer, FLAT, DEBUG, WX, WY, true><<<grid, WX * WY * 32, 0, s>>>(a);
+  else render_kernel<Tracer, FLAT, DEBUG, WX, WY, false><<<grid, WX * WY * 32, 0, s>>>(a);
   return cudaGetLastError();
 }
 
