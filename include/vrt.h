@@ -190,11 +190,18 @@ typedef struct vrt_grid_info {
 } vrt_grid_info;
 int vrt_grid_info_get(vrt_ctx* ctx, vrt_grid_info* out);
 int vrt_read_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count); /* count must be cells_total */
+/* The sun field of the last render (VRT_OPT_SUN_FIELD): one array of (size+2)^3 cells in the same format, whose radius is the larger of
+ * the sun octant's radius and what the TUBE of the cell along the sun direction allows (the cells a ray from anywhere in the cell can
+ * touch while it travels k cells along the dominant axis of the direction). */
+int vrt_read_sun_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count);
 
-/* Tuning options; 1 and 2 take effect at the next vrt_upload_grid, 3 at the next render. */
+/* Tuning options; 1 and 2 take effect at the next vrt_upload_grid, 3 and 4 at the next render. */
 enum {
   VRT_OPT_OCTANT_FIELDS = 1, /* 1 (default) = eight direction-octant radius fields, 0 = one isotropic field */
   VRT_OPT_RADIUS_CAP = 2,    /* 1..255 = cap of the stored empty radius, 0 (default) = 255 up to 256^3, 96 above (build time is O(radius) per voxel) */
+  VRT_OPT_SUN_FIELD = 4,     /* the radius field the SHADOW rays walk: 1 (default) = for chunks up to 256^3 a field built for the frame's sun direction
+                                (every shadow ray points at the sun, voxel.glsl:191-201; rebuilt on the render stream whenever u_SunDir changes,
+                                one more (size+2)^3 uint16 array); 2 = for every chunk size; 0 = shadow rays walk the sun's octant field */
   VRT_OPT_HOST_DIRECT = 3    /* 1 (default) = vrt_render_host into PINNED host memory lets the render kernel store the pixels straight
                                 into it over PCIe (no device frame, no copy); 0 = always render to the device frame, then copy */
 };

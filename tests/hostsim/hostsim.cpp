@@ -116,6 +116,41 @@ int hostsim_build_cells_oct(const uint8_t* grid, int n, int cap, uint16_t* cells
 
 }  // extern "C"
 
+// The sun field (rt_common.cuh), host statement: same definition, plain loops over unpadded coordinates.
+static void build_sun_cells(const uint16_t* base, int n, const V3& sun, std::vector<uint16_t>& out) {
+  const int P = n + 2;
+  SunTube t;
+  make_sun_tube(t, sun);
+  out.assign(base, base + (size_t)P * P * P);
+  auto at = [P](const int c[3]) { return (size_t)(c[0] + 1) + (size_t)(c[1] + 1) * P + (size_t)(c[2] + 1) * P * P; };
+  auto in = [n](int v) { return v >= 0 && v < n; };
+  int c[3];
+  for (c[2] = 0; c[2] < n; c[2]++)
+    for (c[1] = 0; c[1] < n; c[1]++)
+      for (c[0] = 0; c[0] < n; c[0]++) {
+        const uint16_t v = base[at(c)];
+        int r = v >> 8;
+        if ((v & 0xFF) || r > kSunLayers) continue;
+        int free_layers = 0;                                   // number of leading tube layers without an occupied cell
+        for (int j = 0; j <= kSunLayers; j++, free_layers++) {
+          int q[3];
+          q[t.dom] = c[t.dom] + t.sgn[t.dom] * j;
+          bool blocked = false;
+          if (in(q[t.dom]))
+            for (int l1 = t.lo1[j]; l1 <= t.hi1[j] && !blocked; l1++)
+              for (int l2 = t.lo2[j]; l2 <= t.hi2[j] && !blocked; l2++) {
+                q[t.lat1] = c[t.lat1] + t.sgn[t.lat1] * l1;
+                q[t.lat2] = c[t.lat2] + t.sgn[t.lat2] * l2;
+                if (in(q[t.lat1]) && in(q[t.lat2]) && (base[at(q)] & 0xFF)) blocked = true;
+              }
+          if (blocked) break;
+        }
+        if (free_layers > r) r = free_layers;                  // layers 0..G free -> radius G + 1 = their number
+        if (r == 2 && (c[0] == (t.sgn[0] > 0 ? n - 1 : 0) || c[1] == (t.sgn[1] > 0 ? n - 1 : 0) || c[2] == (t.sgn[2] > 0 ? n - 1 : 0))) r = 1;
+        out[at(c)] = (uint16_t)((r << 8) | (v & 0xFF));
+      }
+}
+
 template <class Tracer, bool FLAT>
 static void render_rows(const FrameArgs& f, std::atomic<int>& next, float* out_f32, uint8_t* out_rgba8, uint32_t* out_hit,
                         uint8_t* out_bounces, uint64_t* counters) {
@@ -159,6 +194,19 @@ int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cel
   f.oct_stride = octants ? (size_t)(p->size + 2) * (p->size + 2) * (p->size + 2) : 0;
   f.rows_local = (int)(vrt_tile_pixels(p) / p->tile_w);
   if (!finish_frame_args(f)) return -1;
+  // what vrt_render does by default for chunks up to 256^3 (VRT_OPT_SUN_FIELD = 1): shadow rays walk the sun field
+  static std::vector<uint16_t> sun_field;
+  static const uint16_t* sun_key_base = nullptr; static float sun_key[3] = {0, 0, 0}; static int sun_key_n = 0;
+  static uint64_t sun_key_sum = 0;
+  if (mode == 1 && p->size <= 256 && !getenv("HOSTSIM_NO_SUN_FIELD")) {
+    uint64_t sum = 0;                                        // the caller may reuse the buffer for another grid
+    { const size_t p3 = (size_t)(p->size + 2) * (p->size + 2) * (p->size + 2); for (size_t i = 0; i < p3; i += 97) sum = sum * 1315423911ull + f.sun_cells[i]; }
+    if (sun_key_base != f.sun_cells || sun_key_n != p->size || sun_key_sum != sum || sun_key[0] != f.sun_unit.x || sun_key[1] != f.sun_unit.y || sun_key[2] != f.sun_unit.z) {
+      build_sun_cells(f.sun_cells, p->size, f.sun_unit, sun_field);
+      sun_key_base = f.sun_cells; sun_key_n = p->size; sun_key_sum = sum; sun_key[0] = f.sun_unit.x; sun_key[1] = f.sun_unit.y; sun_key[2] = f.sun_unit.z;
+    }
+    f.sun_cells = sun_field.data();
+  }
   bool flat = (p->flags & VRT_FLAG_COLOR_ONLY) != 0;
   const bool noisy = f.careful != 0;                       // what launch_render looks at (kernels.cu)
   bool glass = false;                                      // any voxel of material 2 (what vrt_upload_grid counts)
@@ -183,6 +231,47 @@ int hostsim_render(const vrt_params* p, const uint8_t* grid, const uint16_t* cel
   for (auto& t : th) t.join();
   if (counters) std::memcpy(counters, cnt, sizeof(cnt));
   return 0;
+}
+
+// Builds the sun field for `sun` from the octant arrays (as hostsim_build_cells_oct made them) into out ((n+2)^3).
+int hostsim_build_sun_cells(const uint16_t* cells_oct, int n, int octants, const float sun[3], uint16_t* out) {
+  DirConst k;
+  V3 s = normalize3(mk3(sun[0], sun[1], sun[2]));
+  set_dir_const(k, s, n + 2);
+  const size_t p3 = (size_t)(n + 2) * (n + 2) * (n + 2);
+  std::vector<uint16_t> v;
+  build_sun_cells(cells_oct + (octants ? (size_t)k.oct * p3 : 0), n, s, v);
+  std::memcpy(out, v.data(), p3 * sizeof(uint16_t));
+  return 0;
+}
+
+// Property check of a sun field, independent of how it was built: from `samples` random points in random empty cells, follow the ray
+// along `sun` with a plain one-cell-at-a-time walk for as long as the cell's radius lets a jump travel (dominant travel r - 1 - 1/64);
+// every cell touched on the way must be empty.  Returns the number of violations.
+int hostsim_check_sun_cells(const uint16_t* field, int n, const float sun[3], int samples, uint32_t seed) {
+  const int P = n + 2;
+  V3 s = normalize3(mk3(sun[0], sun[1], sun[2]));
+  const float d[3] = {s.x, s.y, s.z};
+  const float dmax = fmaxf(fabsf(d[0]), fmaxf(fabsf(d[1]), fabsf(d[2])));
+  auto rnd = [&seed]() { seed = seed * 1664525u + 1013904223u; return (seed >> 8) * (1.0f / 16777216.0f); };
+  int bad = 0;
+  for (int it = 0; it < samples; it++) {
+    int c[3] = {(int)(rnd() * n), (int)(rnd() * n), (int)(rnd() * n)};
+    const uint16_t v = field[(size_t)(c[0] + 1) + (size_t)(c[1] + 1) * P + (size_t)(c[2] + 1) * P * P];
+    const int r = v >> 8;
+    if ((v & 0xFF) || r < 2) continue;
+    double o[3] = {c[0] + rnd(), c[1] + rnd(), c[2] + rnd()};
+    const double tend = (r - 1.0 - 1.0 / 64.0) / dmax;          // time of the jump's landing point
+    const int steps = 4000;
+    for (int q = 0; q <= steps; q++) {                           // dense sampling of the segment (cells are 1 wide, step << 1)
+      const double t = tend * q / steps;
+      int cc[3];
+      bool in = true;
+      for (int a = 0; a < 3; a++) { cc[a] = (int)floor(o[a] + t * d[a]); in = in && cc[a] >= 0 && cc[a] < n; }
+      if (in && (field[(size_t)(cc[0] + 1) + (size_t)(cc[1] + 1) * P + (size_t)(cc[2] + 1) * P * P] & 0xFF)) { bad++; break; }
+    }
+  }
+  return bad;
 }
 
 // 1 if finish_frame_args (the product's per-frame host logic) selects the careful instantiation for these params.

@@ -266,6 +266,34 @@ def test_repack_matches_host_statement(ctx):
         ctx.set_option(vrt.OPT_OCTANT_FIELDS, 1)
 
 
+def test_sun_field_matches_host_statement_and_follows_the_sun(ctx):
+    """VRT_OPT_SUN_FIELD (default on up to 256^3): the device-built field equals the host statement for several sun directions, is
+    rebuilt when u_SunDir changes (and only then), and switching it off changes no hit map and (almost) no pixel."""
+    import ctypes as C
+    from common import hostsim_lib
+    grid, n, atlas, ts = upload(ctx, "terrain128")
+    cells = hostsim_cells(grid, n, 1)
+    launches = ctx.kernel_launches()
+    for tod in (0.0, 7.0, 19.0, 33.0):
+        p = make_params(320, 180, "terrain128", "terrain_low", time_of_day=tod)
+        ctx.render(p); ctx.render(p)
+        assert ctx.kernel_launches() - launches == 3          # one build + two renders
+        launches = ctx.kernel_launches()
+        want = np.zeros((n + 2) ** 3, np.uint16)
+        s3 = (C.c_float * 3)(*[float(x) for x in p.sunDir])
+        hostsim_lib().hostsim_build_sun_cells(cells.ctypes.data_as(C.c_void_p), n, 1, s3, want.ctypes.data_as(C.c_void_p))
+        assert np.array_equal(ctx.read_sun_cells(), want), tod
+    p = make_params(960, 540, "terrain128", "terrain_low")
+    a = gpu_render(ctx, p)
+    try:
+        ctx.set_option(vrt.OPT_SUN_FIELD, 0)
+        b = gpu_render(ctx, p)
+    finally:
+        ctx.set_option(vrt.OPT_SUN_FIELD, 1)
+    assert np.array_equal(a.hit, b.hit) and int((a.rgba8 != b.rgba8).any(axis=1).sum()) <= 2
+    assert a.counters["actual_steps"] < b.counters["actual_steps"]
+
+
 def test_isotropic_field_option_renders_within_caps(ctx):
     """VRT_OPT_OCTANT_FIELDS = 0 (one isotropic radius field) is still a valid traversal; device == host simulation."""
     try:

@@ -156,6 +156,37 @@ def test_lattice_line_eye_with_an_aligned_view_is_careful_and_generic_views_stay
         assert hostsim_lib().hostsim_frame_is_careful(C.byref(make_params(1920, 1080, "terrain128", pose))) == 0, pose
 
 
+def test_sun_field_is_conservative_and_changes_no_pixel():
+    """The sun field (rt_common.cuh): (1) property check independent of its construction - from random points of random empty cells a
+    ray along the sun direction touches no occupied cell for as long as the cell's radius lets a jump travel; (2) it never promises
+    less than the octant field it is built from; (3) frames rendered with it equal the frames rendered with the octant field (the same
+    cells are tested, fewer are looked at), with fewer loop iterations."""
+    import os
+    lib = hostsim_lib()
+    for sc in ("terrain128", "refraction128", "glass_cube32"):
+        grid, n, atlas, ts = scene(sc)
+        cells = hostsim_cells(grid, n, 1)
+        for sun in ((0.0, 1.0, 0.2), (0.3, 0.5, -0.8), (-1.0, 0.01, 0.0), (0.577, 0.577, 0.577), (0.0, -0.3, 1.0)):
+            out = np.zeros((n + 2) ** 3, np.uint16)
+            s3 = (C.c_float * 3)(*sun)
+            assert lib.hostsim_build_sun_cells(cells.ctypes.data_as(C.c_void_p), n, 1, s3, out.ctypes.data_as(C.c_void_p)) == 0
+            assert lib.hostsim_check_sun_cells(out.ctypes.data_as(C.c_void_p), n, s3, 60000, 4242) == 0, (sc, sun)
+            o = (1 if sun[0] < 0 else 0) | (2 if sun[1] < 0 else 0) | (4 if sun[2] < 0 else 0)
+            base = cells.reshape(8, -1)[o]
+            assert np.array_equal(out & 0xFF, base & 0xFF) and ((out >> 8) >= (base >> 8)).all()
+    for sc, pose in (("terrain128", "terrain_low"), ("refraction128", "refraction_close"), ("terrain32", "terrain32_above")):
+        grid, n, atlas, ts = scene(sc)
+        p = make_params(480, 270, sc, pose)
+        with_field = hostsim_render(p, grid, atlas, 1)
+        os.environ["HOSTSIM_NO_SUN_FIELD"] = "1"
+        try:
+            without = hostsim_render(p, grid, atlas, 1)
+        finally:
+            del os.environ["HOSTSIM_NO_SUN_FIELD"]
+        assert int((with_field.rgba8 != without.rgba8).any(axis=1).sum()) <= 2 and np.array_equal(with_field.hit, without.hit)
+        assert with_field.counters["actual_steps"] < without.counters["actual_steps"]
+
+
 def test_randomised_poses_terminate_and_exact_replay_stays_bit_exact():
     """A slice of tools/fuzz_hostsim.py: random cameras inside / around / on the chunk, random caps and bounce limits.  Every
     case runs in its own process under a timeout (a walk that never ends is a failure, not a hang of the suite)."""

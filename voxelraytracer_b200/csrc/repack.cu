@@ -112,6 +112,55 @@ __global__ void __launch_bounds__(256) pack_cells(const uint8_t* __restrict__ gr
   }
 }
 
+// The sun field (rt_common.cuh): base = the radius field shadow rays would otherwise walk (the sun octant's array).  One thread per
+// padded cell, x fastest.  Occupied cells, border cells and cells whose radius already exceeds what the tube search can give are
+// copied; the others search their tube layer by layer until an occupied cell turns up.
+__global__ void __launch_bounds__(256) sun_field_kernel(const uint16_t* __restrict__ base, uint16_t* __restrict__ out, int n, const __grid_constant__ SunTube t) {
+  const int P = n + 2;
+  const size_t total = (size_t)P * P * P;
+  const int stride[3] = {1, P, P * P};
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const unsigned v = __ldg(base + i);
+    unsigned r = v >> 8;
+    int c[3] = {(int)(i % P) - 1, (int)((i / P) % P) - 1, (int)(i / ((size_t)P * P)) - 1};
+    const bool inside = (unsigned)c[0] < (unsigned)n && (unsigned)c[1] < (unsigned)n && (unsigned)c[2] < (unsigned)n;
+    if (inside && (v & 0xFFu) == 0u && r <= (unsigned)kSunLayers) {
+      int G = -1;
+      for (int j = 0; j <= kSunLayers; j++) {
+        const int cd = c[t.dom] + t.sgn[t.dom] * j;
+        bool blocked = false;
+        if ((unsigned)cd < (unsigned)n) {                   // a layer outside the chunk is empty space
+          for (int l2 = t.lo2[j]; l2 <= t.hi2[j] && !blocked; l2++) {
+            const int c2 = c[t.lat2] + t.sgn[t.lat2] * l2;
+            if ((unsigned)c2 >= (unsigned)n) continue;
+            for (int l1 = t.lo1[j]; l1 <= t.hi1[j]; l1++) {
+              const int c1 = c[t.lat1] + t.sgn[t.lat1] * l1;
+              if ((unsigned)c1 >= (unsigned)n) continue;
+              const size_t q = (size_t)(cd + 1) * stride[t.dom] + (size_t)(c1 + 1) * stride[t.lat1] + (size_t)(c2 + 1) * stride[t.lat2];
+              if (__ldg(base + q) & 0xFFu) { blocked = true; break; }
+            }
+          }
+        }
+        if (blocked) break;
+        G = j;
+      }
+      unsigned rd = (unsigned)(G + 1);
+      if (rd > r) r = rd;
+      // radius 2 = two steps without a look in between: not next to the one-cell border (see pack_cells)
+      if (r == 2u && (c[0] == (t.sgn[0] > 0 ? n - 1 : 0) || c[1] == (t.sgn[1] > 0 ? n - 1 : 0) || c[2] == (t.sgn[2] > 0 ? n - 1 : 0))) r = 1u;
+    }
+    out[i] = (uint16_t)((r << 8) | (v & 0xFFu));
+  }
+}
+
+cudaError_t launch_sun_field(const uint16_t* d_base, uint16_t* d_out, int n, const SunTube& tube, cudaStream_t stream) {
+  const size_t ptotal = (size_t)(n + 2) * (n + 2) * (n + 2);
+  size_t want = (ptotal + 255) / 256;
+  const unsigned blocks = (unsigned)(want > 148u * 64u ? 148u * 64u : want);
+  sun_field_kernel<<<blocks, 256, 0, stream>>>(d_base, d_out, n, tube);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_repack(const uint8_t* d_grid, int n, int radius_cap, uint8_t* tmp_a, uint8_t* tmp_b, uint16_t* d_cells,
                           unsigned long long* d_stats, cudaStream_t stream, int* launches) {
   int log2n = 0;

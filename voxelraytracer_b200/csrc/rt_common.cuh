@@ -194,6 +194,41 @@ VRT_HD void set_dir_const(DirConst& w, const V3& d, int P) {
   w.oct = (d.x < 0.0f ? 1 : 0) | (d.y < 0.0f ? 2 : 0) | (d.z < 0.0f ? 4 : 0);
 }
 
+// ---- the sun field: a radius field for ONE direction ------------------------------------------------------------------------
+// Every shadow ray of a frame points at the sun (voxel.glsl:191-201), so the array the shadow walk reads can promise more than the
+// octant field does.  The octant radius of a cell is limited by ANY occupied cell in its forward box; a ray along s only ever touches
+// the "tube" of its cell: after t cells of travel along the dominant axis D it has moved t * |s_L / s_D| along a lateral axis L.  A
+// shadow ray that leaves a wall or a slope sideways to the sun keeps radius 1 in the octant field for as long as the wall is a
+// forward neighbour (15 loop iterations per shadow ray on the refraction scene) - the tube does not contain the wall at all.
+//   layer j of the tube of cell c = the cells with dominant offset j that a ray starting ANYWHERE in c can touch: its travel while in
+//   layer j lies in [max(0, j - 1), j + 1), so the lateral offset lies in [lo, hi] = [floor(max(0, j - 1) a), ceil(1 + (j + 1) a + m) - 1]
+//   with a = |s_L / s_D| and m = 1e-3 cells of margin for the float position arithmetic of the walk (a == 0 exactly: offset 0 only -
+//   the walk never steps along an axis whose direction component is 0, and derives that cell coordinate from the position alone).
+// If layers 0..G of the tube hold no occupied cell, a jump of dominant travel < G stays inside them, so the cell may carry radius
+// G + 1 (rt_trace_fast.cuh: a jump advances by r - 1 - 1/64).  The sun field stores max(octant radius, G + 1), G searched up to
+// kSunLayers; cells whose octant radius is already larger are copied.  Built on the device whenever the sun direction changes
+// (repack.cu, ~cells near surfaces x a few dozen loads), restated on the host in tests/hostsim.
+constexpr int kSunLayers = 24;
+struct SunTube {
+  int dom, lat1, lat2;                 // dominant and lateral axes (0, 1, 2 = x, y, z)
+  int sgn[3];                          // +1 / -1 per axis: the octant of s (a zero component counts as +, like DirConst::oct)
+  signed char lo1[kSunLayers + 1], hi1[kSunLayers + 1], lo2[kSunLayers + 1], hi2[kSunLayers + 1];
+};
+inline void make_sun_tube(SunTube& t, const V3& s) {
+  const double a[3] = {fabs((double)s.x), fabs((double)s.y), fabs((double)s.z)};
+  t.dom = a[0] >= a[1] && a[0] >= a[2] ? 0 : (a[1] >= a[2] ? 1 : 2);
+  t.lat1 = (t.dom + 1) % 3; t.lat2 = (t.dom + 2) % 3;
+  t.sgn[0] = s.x < 0.0f ? -1 : 1; t.sgn[1] = s.y < 0.0f ? -1 : 1; t.sgn[2] = s.z < 0.0f ? -1 : 1;
+  const double al1 = a[t.dom] > 0.0 ? a[t.lat1] / a[t.dom] : 0.0, al2 = a[t.dom] > 0.0 ? a[t.lat2] / a[t.dom] : 0.0;
+  for (int j = 0; j <= kSunLayers; j++) {
+    const double t0 = j > 1 ? (double)(j - 1) : 0.0, t1 = (double)(j + 1);
+    t.lo1[j] = (signed char)(al1 > 0.0 ? (int)floor(t0 * al1) : 0);
+    t.lo2[j] = (signed char)(al2 > 0.0 ? (int)floor(t0 * al2) : 0);
+    t.hi1[j] = (signed char)(al1 > 0.0 ? (int)ceil(1.0 + t1 * al1 + 1e-3) - 1 : 0);
+    t.hi2[j] = (signed char)(al2 > 0.0 ? (int)ceil(1.0 + t1 * al2 + 1e-3) - 1 : 0);
+  }
+}
+
 // Everything a pixel needs, passed by value as a __grid_constant__ kernel parameter.
 struct FrameArgs {
   vrt_params p;
@@ -214,7 +249,8 @@ struct FrameArgs {
   float tex_scale;          // u_AtlasTextureSize / u_AtlasSize (fast traversal's texture coordinates)
   int pitch;                // n + 2
   uint32_t ibias;           // jump index constant (see set_dir_const), per frame so that it is read from the constant bank
-  const uint16_t* sun_cells;  // cells + sun.oct * oct_stride: the array every shadow ray walks
+  const uint16_t* sun_cells;  // the array every shadow ray walks: the sun field when the caller has built one (set before finish_frame_args),
+                              //   else cells + sun.oct * oct_stride
   int rows_local;           // number of compact rows this launch writes
   int log2n;
   int band_shift;           // log2(band_rows) when band_rows is a power of two (frame_row then needs no division), else -1
@@ -336,7 +372,7 @@ inline bool finish_frame_args(FrameArgs& a) {
   set_dir_const(a.sun, a.sun_unit, a.p.size + 2);
   a.pitch = a.p.size + 2;
   a.ibias = a.sun.ibias;
-  a.sun_cells = a.cells ? a.cells + (size_t)a.sun.oct * a.oct_stride : nullptr;
+  if (!a.sun_cells) a.sun_cells = a.cells ? a.cells + (size_t)a.sun.oct * a.oct_stride : nullptr;
   return (1 << a.log2n) == a.p.size;
 }
 

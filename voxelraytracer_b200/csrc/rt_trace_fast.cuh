@@ -209,13 +209,17 @@ struct FastTracer {
       const int a = r.face_axis;
       const bool ax = a == 0, ay = a == 1, az = !ax && !ay;
       const float fnn = (float)n;
-      const float plane = rintf(ax ? r.pos.x : (ay ? r.pos.y : r.pos.z));
-      const float ca = r.face_nsign > 0.0f ? plane : plane - 1.0f;
+      const float pa = ax ? r.pos.x : (ay ? r.pos.y : r.pos.z);
+      const float plane = rintf(pa);
+      const float da = ax ? k.d.x : (ay ? k.d.y : k.d.z);
+      // A ray that runs IN the face plane (direction component exactly 0 - every shadow ray from an x face under the default sun
+      // (0, 1, 0.2)) never crosses it: the reference samples the column its float position lies in (voxel.glsl:328-330), and so does
+      // every jump of this walk (land() floors the position), so the start cell follows the position too, not the face's side.
+      const float ca = da == 0.0f ? floorf(pa) : (r.face_nsign > 0.0f ? plane : plane - 1.0f);
       // face axis: clamp to [-1, n] (the border cells); the others to [0, n-1]
       const float cx = ax ? fminf(fmaxf(ca, -1.0f), fnn) : fminf(fmaxf(floorf(r.pos.x), 0.0f), fn1);
       const float cy = ay ? fminf(fmaxf(ca, -1.0f), fnn) : fminf(fmaxf(floorf(r.pos.y), 0.0f), fn1);
       const float cz = az ? fminf(fmaxf(ca, -1.0f), fnn) : fminf(fmaxf(floorf(r.pos.z), 0.0f), fn1);
-      const float da = ax ? k.d.x : (ay ? k.d.y : k.d.z);
       const float cc = ax ? cx : (ay ? cy : cz);
       const bool into = da != 0.0f && (da > 0.0f) != (r.face_nsign > 0.0f);  // moving against the normal = through the face
       if ((cc < 0.0f || cc > fn1) && !into) return false;                    // on the chunk boundary, heading out

@@ -28,6 +28,11 @@ struct vrt_ctx {
   int octants = 0;                 // what d_cells holds
   int opt_radius_cap = 0;          // VRT_OPT_RADIUS_CAP, 0 = default by chunk size
   int opt_host_direct = 1;         // VRT_OPT_HOST_DIRECT
+  int opt_sun_field = 1;           // VRT_OPT_SUN_FIELD: 0 off, 1 auto (chunks up to 256^3), 2 always
+  uint16_t* d_sun = nullptr;       // the sun field (one more (n+2)^3 array), valid for sun_dir / sun_base
+  float sun_dir[3] = {0, 0, 0};
+  const uint16_t* sun_base = nullptr;
+  int64_t sun_builds = 0;
   const void* tgt_ptr[8] = {nullptr}; bool tgt_remote[8] = {false}; int tgt_next = 0;   // remote_target() cache
   uintptr_t ipc_lo[8] = {0}, ipc_hi[8] = {0}; int ipc_n = 0;                           // address ranges mapped by vrt_ipc_open
   // atlas
@@ -142,7 +147,7 @@ int vrt_destroy(vrt_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   cudaFree(ctx->d_grid); cudaFree(ctx->d_cells); cudaFree(ctx->d_atlas); cudaFree(ctx->d_fb); cudaFree(ctx->d_f32);
-  cudaFree(ctx->d_hit); cudaFree(ctx->d_bounces); cudaFree(ctx->d_counters); cudaFree(ctx->d_tickets);
+  cudaFree(ctx->d_hit); cudaFree(ctx->d_bounces); cudaFree(ctx->d_counters); cudaFree(ctx->d_tickets); cudaFree(ctx->d_sun);
   for (int i = 0; i < vrt_ctx::kTimers; i++) {
     if (ctx->ev0[i]) cudaEventDestroy(ctx->ev0[i]);
     if (ctx->ev1[i]) cudaEventDestroy(ctx->ev1[i]);
@@ -162,6 +167,8 @@ static int repack_locked(vrt_ctx* ctx, int size, cudaStream_t s) {
   const size_t n3 = (size_t)size * size * size, p3 = (size_t)(size + 2) * (size + 2) * (size + 2);
   int oct = ctx->opt_octants ? 1 : 0;
   if (ctx->d_cells) { cudaFree(ctx->d_cells); ctx->d_cells = nullptr; }
+  if (ctx->d_sun) { cudaFree(ctx->d_sun); ctx->d_sun = nullptr; }
+  ctx->sun_base = nullptr;
   uint8_t* tmp = nullptr;                                  // 2 (isotropic) or 3 (octants) scratch volumes of n^3 bytes
   if (oct) {
     // eight fields need 16 (n+2)^3 + 3 n^3 bytes at once (20 GB at 1024^3): if that does not fit, build the single
@@ -335,6 +342,27 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   if (p->flags & VRT_FLAG_COUNTERS) a.counters = ctx->d_counters;
   a.rows_local = (int)(npix / p->tile_w);
   finish_frame_args(a);
+  // The sun field: rebuilt (on this stream, before the render) whenever the sun direction differs from the one it was built for.
+  if (!(p->flags & VRT_FLAG_EXACT) && (ctx->opt_sun_field == 2 || (ctx->opt_sun_field == 1 && ctx->size <= 256))) {
+    const uint16_t* base = a.sun_cells;                      // the sun octant's array (or the isotropic one)
+    if (!ctx->d_sun) {
+      const size_t p3 = (size_t)(ctx->size + 2) * (ctx->size + 2) * (ctx->size + 2);
+      if (cudaMalloc((void**)&ctx->d_sun, p3 * sizeof(uint16_t)) != cudaSuccess) { cudaGetLastError(); ctx->d_sun = nullptr; ctx->warn = "sun field: allocation failed, shadow rays walk the octant field"; }
+    }
+    if (ctx->d_sun) {
+      if (ctx->sun_base != base || ctx->sun_dir[0] != a.sun_unit.x || ctx->sun_dir[1] != a.sun_unit.y || ctx->sun_dir[2] != a.sun_unit.z) {
+        // renders still in flight on other streams may be reading the old field
+        for (int i = 0; i < vrt_ctx::kTimers; i++)
+          if (ctx->timer_last >= 0) CU(cudaStreamWaitEvent(s, ctx->ev1[i], 0));
+        SunTube tube;
+        make_sun_tube(tube, a.sun_unit);
+        CU(launch_sun_field(base, ctx->d_sun, ctx->size, tube, s));
+        ctx->sun_base = base; ctx->sun_dir[0] = a.sun_unit.x; ctx->sun_dir[1] = a.sun_unit.y; ctx->sun_dir[2] = a.sun_unit.z;
+        ctx->launches += 1; ctx->sun_builds += 1;
+      }
+      a.sun_cells = ctx->d_sun;
+    }
+  }
   const int tm = ctx->timer_next;
   ctx->timer_next = (tm + 1) % vrt_ctx::kTimers;
   CU(cudaEventRecord(ctx->ev0[tm], s));
@@ -471,11 +499,26 @@ int vrt_read_cells(vrt_ctx* ctx, uint16_t* host, size_t count) {
   return VRT_OK;
 }
 
+int vrt_read_sun_cells(vrt_ctx* ctx, uint16_t* host, size_t count) {
+  if (!ctx || !host) return fail(ctx, VRT_E_INVALID, "vrt_read_sun_cells: NULL argument");
+  if (!ctx->d_sun || !ctx->sun_base) return fail(ctx, VRT_E_NOT_READY, "vrt_read_sun_cells: no sun field built yet (render a frame first; VRT_OPT_SUN_FIELD)");
+  const size_t p3 = (size_t)(ctx->size + 2) * (ctx->size + 2) * (ctx->size + 2);
+  if (count != p3) return fail(ctx, VRT_E_INVALID, "vrt_read_sun_cells: count %zu != (size+2)^3 = %zu", count, p3);
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy(host, ctx->d_sun, p3 * sizeof(uint16_t), cudaMemcpyDeviceToHost));
+  return VRT_OK;
+}
+
 int vrt_set_option(vrt_ctx* ctx, int option, int value) {
   if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_set_option: NULL ctx");
   switch (option) {
     case VRT_OPT_OCTANT_FIELDS: ctx->opt_octants = value ? 1 : 0; return VRT_OK;
     case VRT_OPT_HOST_DIRECT: ctx->opt_host_direct = value ? 1 : 0; return VRT_OK;
+    case VRT_OPT_SUN_FIELD:
+      if (value < 0 || value > 2) return fail(ctx, VRT_E_INVALID, "vrt_set_option: sun field mode %d not in [0,2]", value);
+      ctx->opt_sun_field = value; return VRT_OK;
     case VRT_OPT_RADIUS_CAP:
       if (value < 0 || value > 255) return fail(ctx, VRT_E_INVALID, "vrt_set_option: radius cap %d not in [0,255]", value);
       ctx->opt_radius_cap = value; return VRT_OK;

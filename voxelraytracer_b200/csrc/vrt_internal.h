@@ -23,6 +23,9 @@ cudaError_t launch_repack(const uint8_t* d_grid, int n, int radius_cap, uint8_t*
 cudaError_t launch_repack_octants(const uint8_t* d_grid, int n, int radius_cap, uint8_t* tmp_a, uint8_t* tmp_b, uint8_t* tmp_c,
                                   uint16_t* d_cells, unsigned long long* d_stats, cudaStream_t stream, int* launches);
 
+// The sun field: base radius field (the sun octant's array) -> max(base radius, tube radius), see rt_common.cuh.
+cudaError_t launch_sun_field(const uint16_t* d_base, uint16_t* d_out, int n, const SunTube& tube, cudaStream_t stream);
+
 // temporal.cu
 cudaError_t launch_read_probe(const void* d_buf, size_t bytes, int passes, int num_sms, unsigned int* sink, cudaStream_t stream);
 cudaError_t launch_temporal_blend(const uint8_t* d_new, const uint8_t* d_old, uint8_t* d_out, int64_t npix, float alpha, cudaStream_t stream);
