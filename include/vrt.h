@@ -200,8 +200,10 @@ enum {
   VRT_OPT_OCTANT_FIELDS = 1, /* 1 (default) = eight direction-octant radius fields, 0 = one isotropic field */
   VRT_OPT_RADIUS_CAP = 2,    /* 1..255 = cap of the stored empty radius, 0 (default) = 255 up to 256^3, 96 above (build time is O(radius) per voxel) */
   VRT_OPT_SUN_FIELD = 4,     /* the radius field the SHADOW rays walk: 1 (default) = for chunks up to 256^3 a field built for the frame's sun direction
-                                (every shadow ray points at the sun, voxel.glsl:191-201; rebuilt on the render stream whenever u_SunDir changes,
-                                one more (size+2)^3 uint16 array); 2 = for every chunk size; 0 = shadow rays walk the sun's octant field */
+                                (every shadow ray points at the sun, voxel.glsl:191-201; one more (size+2)^3 uint16 array, built on the render stream on
+                                the second consecutive frame with the same u_SunDir - ~0.3 ms at 128^3 - so a sun that moves every frame, the
+                                reference's day / night cycle, never pays for it); 2 = for every chunk size, rebuilt at once whenever u_SunDir
+                                changes; 0 = shadow rays walk the sun's octant field.  Same pixels in every mode. */
   VRT_OPT_HOST_DIRECT = 3    /* 1 (default) = vrt_render_host into PINNED host memory lets the render kernel store the pixels straight
                                 into it over PCIe (no device frame, no copy); 0 = always render to the device frame, then copy */
 };

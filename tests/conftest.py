@@ -28,5 +28,8 @@ def _built():
 def ctx():
     import voxelraytracer_b200 as vrt
     c = vrt.Context(0)
+    # Tests render ONE frame per pose and compare loop-iteration counts with the host simulation, which always walks the sun field:
+    # build it at once instead of on the second frame with the same sun (the default, VRT_OPT_SUN_FIELD = 1; tested on its own).
+    c.set_option(vrt.OPT_SUN_FIELD, 2)
     yield c
     c.close()

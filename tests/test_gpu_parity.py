@@ -111,6 +111,7 @@ def test_c5_big_chunks_against_the_oracle(ctx, sc, W, H, max_len, scale, lean_ca
     traversal that does not accumulate the same error: 3e-3 cells of drift in the reference's hit point are 0.4 texels of the 128^2
     tiles, so a good part of the pixels sample a neighbouring texel (measured RMS 1.0-1.3/255 with CAREFUL, 1.0-1.5 lean)."""
     import common
+    ctx.set_option(vrt.OPT_SUN_FIELD, 1)       # the default: no sun field above 256^3
     grid, n, atlas, ts = upload(ctx, sc)
     info = ctx.grid_info()
     assert info.radius_cap == 96 and info.octants == 8 and ctx.last_warning() == ""
@@ -134,6 +135,7 @@ def test_c5_big_chunks_against_the_oracle(ctx, sc, W, H, max_len, scale, lean_ca
         assert (rms255(c.rgba8, o.rgba8) <= lean_cap[1]).all(), rms255(c.rgba8, o.rgba8)
         assert c.counters["actual_steps"] * 4 < ref_steps          # the replay stays the exception
     common._scene_cache.pop(sc, None)          # 1 GiB of host memory
+    ctx.set_option(vrt.OPT_SUN_FIELD, 2)
 
 
 NOISE_CASES = [
@@ -271,25 +273,27 @@ def test_sun_field_matches_host_statement_and_follows_the_sun(ctx):
     rebuilt when u_SunDir changes (and only then), and switching it off changes no hit map and (almost) no pixel."""
     import ctypes as C
     from common import hostsim_lib
+    ctx.set_option(vrt.OPT_SUN_FIELD, 1)
     grid, n, atlas, ts = upload(ctx, "terrain128")
     cells = hostsim_cells(grid, n, 1)
     launches = ctx.kernel_launches()
     for tod in (0.0, 7.0, 19.0, 33.0):
         p = make_params(320, 180, "terrain128", "terrain_low", time_of_day=tod)
-        ctx.render(p); ctx.render(p)
-        assert ctx.kernel_launches() - launches == 3          # one build + two renders
+        ctx.render(p); ctx.render(p); ctx.render(p)
+        assert ctx.kernel_launches() - launches == 4          # three renders + one build (on the second frame with the same sun)
         launches = ctx.kernel_launches()
         want = np.zeros((n + 2) ** 3, np.uint16)
         s3 = (C.c_float * 3)(*[float(x) for x in p.sunDir])
         hostsim_lib().hostsim_build_sun_cells(cells.ctypes.data_as(C.c_void_p), n, 1, s3, want.ctypes.data_as(C.c_void_p))
         assert np.array_equal(ctx.read_sun_cells(), want), tod
     p = make_params(960, 540, "terrain128", "terrain_low")
+    gpu_render(ctx, p)
     a = gpu_render(ctx, p)
     try:
         ctx.set_option(vrt.OPT_SUN_FIELD, 0)
         b = gpu_render(ctx, p)
     finally:
-        ctx.set_option(vrt.OPT_SUN_FIELD, 1)
+        ctx.set_option(vrt.OPT_SUN_FIELD, 2)
     assert np.array_equal(a.hit, b.hit) and int((a.rgba8 != b.rgba8).any(axis=1).sum()) <= 2
     assert a.counters["actual_steps"] < b.counters["actual_steps"]
 

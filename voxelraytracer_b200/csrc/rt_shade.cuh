@@ -179,14 +179,27 @@ VRT_HD Hit trace_with_shadow(typename Tracer::Ctx& cx, Ray& r, V3& color) {
     s.ntrans = 0;
     s.face_axis = h.axis;
     s.face_nsign = h.nsign;
-    bool shadowed = Tracer::shadow(cx, s, h);
     float brightness = 0.3f;  // ambient (voxel.glsl:91)
-    if (!shadowed) {
+    if (Tracer::Ctx::kLean) {
+      // The shadow ray only decides whether diffuse + specular are added (voxel.glsl:403-415).  Where both are exactly 0 - a face
+      // turned away from the sun whose mirrored sun direction points away from the viewer: n.s <= 0 and reflect(s, n).dir <= 0,
+      // pow(0, e) = 0 - the brightness is (0.3 + 0) + 0 = 0.3 either way, bit for bit, and the walk towards the sun is not taken.
       MatProps m = material_of<FLAT>(h.voxel);
       V3 n = cx.normal_of(h);
-      float diffuse = m.kd * gmax(dot3(n, s.dir), 0.0f);
-      float specular = m.ks * cx.pow_pos(gmax(dot3(reflect3(s.dir, n), r.dir), 0.0f), m.ke);
-      brightness = (0.3f + diffuse) + specular;
+      const float lit = gmax(dot3(n, s.dir), 0.0f), gloss = gmax(dot3(reflect3(s.dir, n), r.dir), 0.0f);
+      const float diffuse = m.kd * lit;
+      if (diffuse != 0.0f || (gloss != 0.0f && m.ks != 0.0f)) {
+        if (!Tracer::shadow(cx, s, h)) brightness = (0.3f + diffuse) + m.ks * cx.pow_pos(gloss, m.ke);
+      }
+    } else {
+      bool shadowed = Tracer::shadow(cx, s, h);
+      if (!shadowed) {
+        MatProps m = material_of<FLAT>(h.voxel);
+        V3 n = cx.normal_of(h);
+        float diffuse = m.kd * gmax(dot3(n, s.dir), 0.0f);
+        float specular = m.ks * cx.pow_pos(gmax(dot3(reflect3(s.dir, n), r.dir), 0.0f), m.ke);
+        brightness = (0.3f + diffuse) + specular;
+      }
     }
     float c[4];
     cx.color_of(h, c);
