@@ -52,6 +52,7 @@ def main():
             sys.exit("exists: " + d)
         os.makedirs(d)
         shutil.copytree(CSRC, os.path.join(d, "csrc"), ignore=shutil.ignore_patterns("*.o", "*.log"))
+        shutil.copytree(CSRC, os.path.join(d, "orig"), ignore=shutil.ignore_patterns("*.o", "*.log"))   # what `adopt` diffs against
         # the variant's headers include ../../include/vrt.h relative to csrc: give it one
         os.makedirs(os.path.join(ROOT, "build", "include"), exist_ok=True)
         shutil.copy(os.path.join(ROOT, "include", "vrt.h"), os.path.join(ROOT, "build", "include", "vrt.h"))
@@ -86,10 +87,17 @@ def main():
             bad += 0 if same else 1
         sys.exit(1 if bad else 0)
     elif cmd == "adopt":
-        for f in os.listdir(os.path.join(d, "csrc")):
-            if f.endswith((".cu", ".cuh", ".h", ".cpp")) or f == "Makefile":
-                shutil.copy(os.path.join(d, "csrc", f), os.path.join(CSRC, f))
-        print("adopted", name)
+        # only the files the variant CHANGED, and only if the in-tree file is still what the variant started from
+        for f in sorted(os.listdir(os.path.join(d, "csrc"))):
+            if not (f.endswith((".cu", ".cuh", ".h", ".cpp")) or f == "Makefile"):
+                continue
+            new, orig, cur = (open(os.path.join(x, f)).read() if os.path.exists(os.path.join(x, f)) else None for x in (os.path.join(d, "csrc"), os.path.join(d, "orig"), CSRC))
+            if new == orig:
+                continue
+            if cur != orig:
+                sys.exit("REFUSED: %s changed in-tree since the variant was made; merge by hand" % f)
+            shutil.copy(os.path.join(d, "csrc", f), os.path.join(CSRC, f))
+            print("adopted", f)
     else:
         sys.exit(__doc__)
 

@@ -363,7 +363,7 @@ inline bool finish_frame_args(FrameArgs& a) {
       }
     }
     const bool noisy = a.p.rayNoise != 0.0f || a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f;
-    a.careful = (noisy || hazard || lattice) ? 1 : 0;
+    a.careful = (noisy || hazard || lattice || (a.p.flags & VRT_FLAG_CAREFUL)) ? 1 : 0;
     a.replay_glass = (a.p.reflectionNoise != 0.0f || a.p.refractionNoise != 0.0f) ? 1 : 0;
   }
   a.band_shift = -1;

@@ -180,16 +180,23 @@ VRT_HD Hit trace_with_shadow(typename Tracer::Ctx& cx, Ray& r, V3& color) {
     s.face_axis = h.axis;
     s.face_nsign = h.nsign;
     float brightness = 0.3f;  // ambient (voxel.glsl:91)
+    float c[4];
+    cx.color_of(h, c);
     if (Tracer::Ctx::kLean) {
-      // The shadow ray only decides whether diffuse + specular are added (voxel.glsl:403-415).  Where both are exactly 0 - a face
-      // turned away from the sun whose mirrored sun direction points away from the viewer: n.s <= 0 and reflect(s, n).dir <= 0,
-      // pow(0, e) = 0 - the brightness is (0.3 + 0) + 0 = 0.3 either way, bit for bit, and the walk towards the sun is not taken.
-      MatProps m = material_of<FLAT>(h.voxel);
-      V3 n = cx.normal_of(h);
-      const float lit = gmax(dot3(n, s.dir), 0.0f), gloss = gmax(dot3(reflect3(s.dir, n), r.dir), 0.0f);
-      const float diffuse = m.kd * lit;
-      if (diffuse != 0.0f || (gloss != 0.0f && m.ks != 0.0f)) {
-        if (!Tracer::shadow(cx, s, h)) brightness = (0.3f + diffuse) + m.ks * cx.pow_pos(gloss, m.ke);
+      // The shadow ray only decides whether diffuse + specular are added to the brightness (voxel.glsl:403-415), and the brightness
+      // only scales texel.rgb * texel.a (voxel.glsl:186-187).  Two cases in which the walk towards the sun cannot change a bit of the
+      // result and is not taken:
+      //  - the texel's alpha is 0 (the see-through part of the glass tile, _COLOR_ONLY glass): rgb * 0 * brightness = 0 whatever it is;
+      //  - diffuse and specular are both exactly 0 - a face turned away from the sun whose mirrored sun direction points away from
+      //    the viewer: n.s <= 0 and reflect(s, n).dir <= 0, pow(0, e) = 0 - so the brightness is (0.3 + 0) + 0 = 0.3 either way.
+      if (c[3] != 0.0f) {
+        MatProps m = material_of<FLAT>(h.voxel);
+        V3 n = cx.normal_of(h);
+        const float lit = gmax(dot3(n, s.dir), 0.0f), gloss = gmax(dot3(reflect3(s.dir, n), r.dir), 0.0f);
+        const float diffuse = m.kd * lit;
+        if (diffuse != 0.0f || (gloss != 0.0f && m.ks != 0.0f)) {
+          if (!Tracer::shadow(cx, s, h)) brightness = (0.3f + diffuse) + m.ks * cx.pow_pos(gloss, m.ke);
+        }
       }
     } else {
       bool shadowed = Tracer::shadow(cx, s, h);
@@ -201,8 +208,6 @@ VRT_HD Hit trace_with_shadow(typename Tracer::Ctx& cx, Ray& r, V3& color) {
         brightness = (0.3f + diffuse) + specular;
       }
     }
-    float c[4];
-    cx.color_of(h, c);
     color = mix3(color, mk3((c[0] * c[3]) * brightness, (c[1] * c[3]) * brightness, (c[2] * c[3]) * brightness), r.energy);
   } else {
     color = mix3(cx.sky(r, color), color, 1.0f - r.energy);

@@ -127,7 +127,10 @@ struct FastTracer {
     if (NOISE) {
       // second-nearest plane time; the pinned recurrence's times carry ~ulp(cumulative length) of error, the walk's ~ulp(t)
       const float second = sx ? fminf(w.tmax.y, w.tmax.z) : (sy ? fminf(w.tmax.x, w.tmax.z) : fminf(w.tmax.x, w.tmax.y));
-      if (second - m <= (w.tol + m) * 1.0e-6f) w.tie = true;
+      // the recurrence adds one rounding of the CUMULATIVE length per step, so its drift grows like sqrt(steps) x ulp(length):
+      // ~1e-4 cells after 100 units, ~3e-3 after 1000 (1024^3 chunks with u_MaxRayLength 2048)
+      const float T = w.tol + m;
+      if (second - m <= T * (1.0e-6f + 1.0e-7f * sqrtf(T))) w.tie = true;
     }
     w.t = m;
     w.inc = sx ? k.dix : (sy ? k.diy : k.diz);
@@ -209,13 +212,13 @@ struct FastTracer {
       const int a = r.face_axis;
       const bool ax = a == 0, ay = a == 1, az = !ax && !ay;
       const float fnn = (float)n;
-      const float pa = ax ? r.pos.x : (ay ? r.pos.y : r.pos.z);
-      const float plane = rintf(pa);
+      const float plane = rintf(ax ? r.pos.x : (ay ? r.pos.y : r.pos.z));
       const float da = ax ? k.d.x : (ay ? k.d.y : k.d.z);
-      // A ray that runs IN the face plane (direction component exactly 0 - every shadow ray from an x face under the default sun
-      // (0, 1, 0.2)) never crosses it: the reference samples the column its float position lies in (voxel.glsl:328-330), and so does
-      // every jump of this walk (land() floors the position), so the start cell follows the position too, not the face's side.
-      const float ca = da == 0.0f ? floorf(pa) : (r.face_nsign > 0.0f ? plane : plane - 1.0f);
+      // (A ray that runs IN the face plane - direction component exactly 0, every shadow ray from an x face under the default sun
+      // (0, 1, 0.2) - is attributed to the empty side of the face like any other.  Following the float position instead, as the
+      // reference's sampling does, was measured: same parity, but half of such rays then crawl through the INSIDE of a glass wall,
+      // C4 glass_wall 0.605 -> 0.658 ms, profiles/r02_ab_face_rule_sun_field.txt.)
+      const float ca = r.face_nsign > 0.0f ? plane : plane - 1.0f;
       // face axis: clamp to [-1, n] (the border cells); the others to [0, n-1]
       const float cx = ax ? fminf(fmaxf(ca, -1.0f), fnn) : fminf(fmaxf(floorf(r.pos.x), 0.0f), fn1);
       const float cy = ay ? fminf(fmaxf(ca, -1.0f), fnn) : fminf(fmaxf(floorf(r.pos.y), 0.0f), fn1);

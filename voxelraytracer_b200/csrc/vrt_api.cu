@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -138,6 +139,7 @@ int vrt_create(int device, vrt_ctx** out) {
     return code;
   }
   ctx->d_stats = ctx->d_counters + CNT_N;
+  if (const char* e = getenv("VRT_SUN_FIELD")) ctx->opt_sun_field = atoi(e) < 0 ? 0 : (atoi(e) > 2 ? 2 : atoi(e));   // tuning override of VRT_OPT_SUN_FIELD
   ctx->num_sms = prop.multiProcessorCount;
   *out = ctx;
   return VRT_OK;
