@@ -93,6 +93,9 @@ def parse():
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl", "none"],
                     help="N>1: p2p = every rank's render kernel stores straight into rank 0's frame over NVLink (fused render+gather); "
                          "nccl = all_gather_into_tensor after the render; none = frames stay on their GPUs")
+    ap.add_argument("--gather-format", default="rgb8", choices=["rgb8", "rgba8"],
+                    help="N>1, p2p gather: pixel format of the frames rank 0 collects - packed RGB8 (the reference's colour attachment, FrameBuffer.cpp:8; "
+                         "25 % fewer bytes over NVLink, default) or the ABI's RGBA8")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: one full frame per GPU per step (pose batch); strong: ONE frame per step, 16-row bands dealt round-robin")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -306,7 +309,8 @@ def run_ours(args):
     gather = args.gather if world > 1 else "none"
     BR = 16
     npix = W * H
-    frame_bytes = npix * 4
+    gbpp = 3 if (gather == "p2p" and args.gather_format == "rgb8") else 4       # bytes per pixel of the gathered frames
+    frame_bytes = npix * gbpp
     if strong:      # ONE frame per step: every rank renders its 16-row bands of the same pose
         full = [mk(common, args.workload, W, H, sc, poses[i % len(poses)], flags) for i in range(len(poses))]
         frames = [sharding.band_params(p, rank, world, BR) for p in full]
@@ -314,6 +318,15 @@ def run_ours(args):
         frames = [mk(common, args.workload, W, H, sc, poses[(i + rank) % len(poses)], flags) for i in range(len(poses))]
     frames = frames[:max(1, min(len(frames), args.steps))]      # only the poses the timed steps will cycle through
     my_pix = vrt.tile_pixels(frames[0])
+
+    def gathered_form(p):
+        """The params of a frame as it is rendered INTO the gather target (packed RGB8 when that is the gather format)."""
+        if gbpp == 4:
+            return p
+        q = p.copy()
+        q.flags |= vrt.FLAG_RGB8_OUT
+        return q
+    gframes = [gathered_form(p) for p in frames]
 
     # reference-equivalent ray / step counts of what THIS rank renders (exact kernel's counters == oracle's, see tests)
     counts = []
@@ -366,14 +379,32 @@ def run_ours(args):
             p2p_base = int(p2p_base.value)
         else:
             gather, p2p_base = "nccl", None
+    # What the gather can reach at best: every rank but 0 copies a frame-sized buffer into its slot of rank 0's memory, all at once
+    # (plain device-to-peer copy kernels, no rendering): aggregate GB/s into rank 0 = the NVLink ingest ceiling of this box.
+    ingest_peak_gbs = None
+    if gather == "p2p":
+        reps = 20
+        src = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
+        dst = _wrap_device(torch, p2p_base + (rank if not strong else 0) * frame_bytes, frame_bytes) if rank != 0 else None
+        torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        if rank != 0:
+            for _ in range(reps):
+                dst.copy_(src)
+        e1.record(); torch.cuda.synchronize()
+        tt = torch.tensor([e0.elapsed_time(e1) / 1e3 if rank != 0 else 0.0], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ingest_peak_gbs = (world - 1) * frame_bytes * reps / float(tt.item()) / 1e9
+        dist.barrier()
     if gather == "nccl":
-        per = sharding.max_rows(H, world, BR) * W * 4 if strong else frame_bytes
+        per = sharding.max_rows(H, world, BR) * W * 4 if strong else frame_bytes          # nccl gather: always RGBA8
         gathered = torch.empty(world * per, dtype=torch.uint8, device="cuda")
         local_fb = [torch.zeros(per, dtype=torch.uint8, device="cuda") for _ in range(2)]
 
     def target(i):
         """(params, device pointer) of step i's output for this rank."""
-        p = frames[i % len(frames)]
+        p = gframes[i % len(frames)]
         if gather == "p2p":
             if strong:
                 q = p.copy()
@@ -418,7 +449,7 @@ def run_ours(args):
         one_step(0, do_flush=False).synchronize()
         torch.cuda.synchronize(); dist.barrier()
         loc = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
-        ctx.render_to(full[0] if strong else frames[0], loc.data_ptr(), None)      # strong: rank-local render of the WHOLE frame
+        ctx.render_to(gathered_form(full[0]) if strong else gframes[0], loc.data_ptr(), None)      # strong: rank-local render of the WHOLE frame
         torch.cuda.synchronize()
         held = _wrap_device(torch, p2p_base, slots * frame_bytes) if (gather == "p2p" and rank == 0) else gathered
         if strong:
@@ -596,6 +627,9 @@ def run_ours(args):
     t_e2e_staged = overlapped(e2e_step)
     e2e_ok = bool(np.array_equal(hosts[(args.steps - 1) % D][0], dbuf[(args.steps - 1) % D].cpu().numpy())) and direct_ok
     # the bound of the overlapped form: the same loop with the render left out (device -> pinned host copies only)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()                               # all ranks copy at the same time: the box's host-ingest ceiling
     t0 = time.perf_counter()
     for i in range(args.steps):
         if i >= D:
@@ -604,6 +638,11 @@ def run_ours(args):
     torch.cuda.synchronize()
     t_copy = time.perf_counter() - t0
 
+    d2h_all = my_pix * 4 * args.steps / t_copy / 1e9
+    if world > 1:      # the host-ingest ceiling of the box: every rank's copies-only leg ran at the same time
+        dd = torch.tensor([d2h_all], dtype=torch.float64, device="cuda")
+        dist.all_reduce(dd, op=dist.ReduceOp.SUM)
+        d2h_all = float(dd.item())
     # max over ranks for times, sum over ranks for work
     if world > 1:
         v = torch.tensor([t_steps, t_kernel, t_e2e_direct, t_pipeline or 0.0, t_e2e_sync, t_e2e_staged, t_sync_staged], dtype=torch.float64, device="cuda")
@@ -701,9 +740,17 @@ def run_ours(args):
                     "rgb8_call": "vrt_render_to into pinned host memory with VRT_FLAG_RGB8_OUT (%d B per step; not the headline: the ABI's default frame is RGBA8)" % (my_pix * 3),
                     "host_frame_check": e2e_ok and rgb_ok,
                     "d2h_only_ms_per_step": 1e3 * t_copy / args.steps, "d2h_only_gbs": my_pix * 4 * args.steps / t_copy / 1e9,
+                    "d2h_only_gbs_all_ranks": d2h_all,
                     "frac_of_d2h_bound": t_copy / t_e2e if world == 1 else None},
             "gpu_launches": int(launches_timed),      # render_kernel launches of rank 0 inside the timed region (one per step)
             "gather_check": gather_check,
+            "gather": None if gather != "p2p" else {
+                "format": "packed RGB8 (the reference's colour attachment format)" if gbpp == 3 else "RGBA8",
+                "bytes_into_rank0_per_step": (world - 1) * frame_bytes if not strong else frame_bytes * (world - 1) // world,
+                "achieved_gbs": ((world - 1) * frame_bytes if not strong else frame_bytes * (world - 1) / world) * args.steps / t_step_total / 1e9,
+                "ingest_peak_gbs": ingest_peak_gbs,
+                "ingest_peak_def": "all other ranks copying frame-sized buffers into rank 0's memory at once (device-to-peer copy kernels, no rendering), measured in this run",
+                "pipelined_gbs": None if not t_pipeline else ((world - 1) * frame_bytes if not strong else frame_bytes * (world - 1) / world) * args.steps / t_pipeline / 1e9},
             "upload_grid_s": t_upload, "radius_fields": "8 direction-octant fields" if args.octants else "1 isotropic field",
             "pipelined": None if not t_pipeline else {"value": rays_all / t_pipeline / 1e6, "unit": "Mrays/s",
                                                        "frames_per_s": frames_total / t_pipeline,
