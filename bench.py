@@ -495,6 +495,8 @@ def run_ours(args):
     launches_timed = ctx.kernel_launches() - launches0
     step_ms = [a.elapsed_time(b) for a, b in ev]
     t_steps = sum(step_ms) / 1e3
+    if os.environ.get("BENCH_DUMP_STEPS"):            # per-rank step times for offline analysis (tools/)
+        np.save(os.path.join(os.environ["BENCH_DUMP_STEPS"], "steps_rank%d.npy" % rank), np.array(step_ms))
 
     # kernel-only windows (for the roofline): the same steps without a gather inside the window
     if gather == "nccl":
