@@ -90,8 +90,10 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
-    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl", "none"],
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "dma", "nccl", "none"],
                     help="N>1: p2p = every rank's render kernel stores straight into rank 0's frame over NVLink (fused render+gather); "
+                         "dma = every rank renders into its own memory and a copy-engine transfer on a side stream puts the pixels into rank 0's frame "
+                         "(overlaps the next frame's render when frames are pipelined); "
                          "nccl = all_gather_into_tensor after the render; none = frames stay on their GPUs")
     ap.add_argument("--gather-format", default="rgb8", choices=["rgb8", "rgba8"],
                     help="N>1, p2p gather: pixel format of the frames rank 0 collects - packed RGB8 (the reference's colour attachment, FrameBuffer.cpp:8; "
@@ -309,7 +311,8 @@ def run_ours(args):
     gather = args.gather if world > 1 else "none"
     BR = 16
     npix = W * H
-    gbpp = 3 if (gather == "p2p" and args.gather_format == "rgb8") else 4       # bytes per pixel of the gathered frames
+    ipc = gather in ("p2p", "dma")                                                # rank 0 owns the gathered frames, the others map them
+    gbpp = 3 if (ipc and args.gather_format == "rgb8") else 4                       # bytes per pixel of the gathered frames
     frame_bytes = npix * gbpp
     if strong:      # ONE frame per step: every rank renders its 16-row bands of the same pose
         full = [mk(common, args.workload, W, H, sc, poses[i % len(poses)], flags) for i in range(len(poses))]
@@ -351,7 +354,7 @@ def run_ours(args):
     local_fb = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(2)]
     gathered = None
     p2p_base = None
-    if gather == "p2p":
+    if ipc:
         # rank 0 owns the gathered frames (double-buffered); the others map them through CUDA IPC and store into them.
         # If the mapping fails on any rank (no peer access between the devices), every rank falls back to the NCCL gather.
         ok = 1
@@ -378,11 +381,11 @@ def run_ours(args):
         if int(flag.item()) == 1:
             p2p_base = int(p2p_base.value)
         else:
-            gather, p2p_base = "nccl", None
+            gather, p2p_base, ipc = "nccl", None, False
     # What the gather can reach at best: every rank but 0 copies a frame-sized buffer into its slot of rank 0's memory, all at once
     # (plain device-to-peer copy kernels, no rendering): aggregate GB/s into rank 0 = the NVLink ingest ceiling of this box.
     ingest_peak_gbs = None
-    if gather == "p2p":
+    if ipc:
         reps = 20
         src = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
         dst = _wrap_device(torch, p2p_base + (rank if not strong else 0) * frame_bytes, frame_bytes) if rank != 0 else None
@@ -413,6 +416,21 @@ def run_ours(args):
             return p, p2p_base + ((i % 2) * world + rank) * frame_bytes
         return p, local_fb[i % 2].data_ptr()
 
+    def dma_gather(i, st):
+        """gather == dma: this rank's pixels of step i, rendered compactly into local_fb, go to rank 0's frame through the copy engines."""
+        src = local_fb[i % 2].data_ptr()
+        if strong:
+            chunk = BR * W * gbpp                                      # one band of rows, contiguous on both sides
+            rows_mine = my_pix // W
+            nb, tail = rows_mine // BR, rows_mine % BR
+            dst = p2p_base + (i % 2) * frame_bytes + rank * chunk
+            if nb:
+                ctx.copy_2d_async(dst, world * chunk, src, chunk, chunk, nb, st.cuda_stream)
+            if tail:                                                    # a last, shorter band
+                ctx.copy_2d_async(dst + nb * world * chunk, world * chunk, src + nb * chunk, chunk, tail * W * gbpp, 1, st.cuda_stream)
+        else:
+            ctx.copy_2d_async(p2p_base + ((i % 2) * world + rank) * frame_bytes, frame_bytes, src, frame_bytes, frame_bytes, 1, st.cuda_stream)
+
     def one_step(i, ev0=None, ev1=None, do_flush=True):
         """flush (untimed) -> [ev0] render (p2p: its stores ARE the gather) (+ nccl gather) [ev1].  Returns the completion event."""
         p, ptr = target(i)
@@ -422,7 +440,7 @@ def run_ours(args):
             if ev0 is not None:
                 ev0.record(stream)
             ctx.render_to(p, ptr, stream.cuda_stream)
-            if ev1 is not None and gather != "nccl":
+            if ev1 is not None and gather not in ("nccl", "dma"):
                 ev1.record(stream)
         done = torch.cuda.Event()
         if gather == "none":
@@ -436,6 +454,11 @@ def run_ours(args):
                 dist.all_gather_into_tensor(gathered, local_fb[i % 2])
                 if ev1 is not None:
                     ev1.record(comm)
+            elif gather == "dma":
+                dma_gather(i, comm)
+                if ev1 is not None:
+                    ev1.record(comm)                 # the window includes this rank's transfer
+                dist.all_reduce(token)
             else:
                 # p2p: 4-byte all-reduce = "every rank's stores of step i have landed in rank 0's frame"; it runs on the
                 # comm stream beside the next step's flush + render and is what rank 0's consumer would wait on
@@ -451,7 +474,7 @@ def run_ours(args):
         loc = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
         ctx.render_to(gathered_form(full[0]) if strong else gframes[0], loc.data_ptr(), None)      # strong: rank-local render of the WHOLE frame
         torch.cuda.synchronize()
-        held = _wrap_device(torch, p2p_base, slots * frame_bytes) if (gather == "p2p" and rank == 0) else gathered
+        held = _wrap_device(torch, p2p_base, slots * frame_bytes) if (ipc and rank == 0) else gathered
         if strong:
             if rank == 0:
                 if gather == "nccl":
@@ -499,7 +522,7 @@ def run_ours(args):
         np.save(os.path.join(os.environ["BENCH_DUMP_STEPS"], "steps_rank%d.npy" % rank), np.array(step_ms))
 
     # kernel-only windows (for the roofline): the same steps without a gather inside the window
-    if gather == "nccl":
+    if gather in ("nccl", "dma"):
         kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
         for i in range(args.steps):
             p, ptr = target(i)
@@ -543,6 +566,9 @@ def run_ours(args):
                     comm.wait_event(rendered)
                     if gather == "nccl":
                         dist.all_gather_into_tensor(gathered, local_fb[i % 2])
+                    elif gather == "dma":
+                        dma_gather(i, comm)
+                        dist.all_reduce(token)
                     else:
                         dist.all_reduce(token)
                     done = torch.cuda.Event(); done.record(comm)
@@ -683,6 +709,8 @@ def run_ours(args):
             ("ONE frame per step split into 16-row bands dealt round-robin over the ranks" if strong else "one frame per GPU per step (pose batch)")
             + ", grid replicated; gather: " + {"p2p": "every rank's render kernel stores its pixels straight into rank 0's frame over NVLink (CUDA IPC mapping), "
                                                       "4-byte NCCL all-reduce per step as the completion signal (overlapped)",
+                                               "dma": "every rank renders into its own memory; a copy-engine transfer on a side stream (cudaMemcpy2DAsync into rank 0's frame, CUDA IPC mapping) "
+                                                      "follows inside the step window and overlaps the next frame's render in the pipelined pass",
                                                "nccl": "all_gather_into_tensor after the render, inside the step window", "none": "none"}[gather])
         # What the timed kernel really executes, from the committed ncu capture of this workload at 1 GPU (per-launch means over the
         # cycled poses); the TIME it is divided by is this run's own CUDA-event time.  Only meaningful when the launches are the
@@ -746,7 +774,8 @@ def run_ours(args):
                     "frac_of_d2h_bound": t_copy / t_e2e if world == 1 else None},
             "gpu_launches": int(launches_timed),      # render_kernel launches of rank 0 inside the timed region (one per step)
             "gather_check": gather_check,
-            "gather": None if gather != "p2p" else {
+            "gather": None if not ipc else {
+                "how": "render kernel's own stores (fused)" if gather == "p2p" else "copy engines after a render into local memory (dma)",
                 "format": "packed RGB8 (the reference's colour attachment format)" if gbpp == 3 else "RGBA8",
                 "bytes_into_rank0_per_step": (world - 1) * frame_bytes if not strong else frame_bytes * (world - 1) // world,
                 "achieved_gbs": ((world - 1) * frame_bytes if not strong else frame_bytes * (world - 1) / world) * args.steps / t_step_total / 1e9,

@@ -229,6 +229,11 @@ int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes
  * With vrt_render_to on the same stream this is the double-buffered form of vrt_render_host: frame i's copy to the host
  * overlaps frame i+1's render on another stream. */
 int vrt_copy_to_host_async(vrt_ctx* ctx, void* host, const void* d_src, size_t bytes, void* stream);
+/* Strided device-to-device copy on `stream` (cudaMemcpy2DAsync through the copy engines; either side may be another GPU's memory mapped
+ * with vrt_ipc_open): `height` chunks of `width_bytes`, `src_pitch` / `dst_pitch` bytes apart.  The band-sharded gather without the
+ * render kernel's remote stores: a rank renders its bands compactly into its own memory and this call puts them at their rows of rank
+ * 0's frame (chunk = band_rows * width * bytes per pixel, dst_pitch = band_count * chunk) while the next frame is being rendered. */
+int vrt_copy_2d_async(vrt_ctx* ctx, void* d_dst, size_t dst_pitch, const void* d_src, size_t src_pitch, size_t width_bytes, size_t height, void* stream);
 
 /* ---- temporal accumulation pass (res/shaders/temporal.glsl:13-19; main.cpp:363-376,388-393) ----
  * acc = alpha * new + (1 - alpha) * acc on RGBA8 device buffers, n pixels.  Channels are blended independently, so a packed

@@ -29,7 +29,7 @@ EXPORTS = [
     "vrt_upload_grid_device", "vrt_upload_atlas", "vrt_render", "vrt_render_to", "vrt_render_host", "vrt_tile_pixels", "vrt_probe_read_gbs",
     "vrt_framebuffer_device", "vrt_read_framebuffer", "vrt_read_debug_maps", "vrt_read_float_frame", "vrt_reset_counters",
     "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells", "vrt_read_sun_cells", "vrt_set_option",
-    "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_host_async", "vrt_copy_to_device", "vrt_temporal_blend", "vrt_temporal_filter",
+    "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_host_async", "vrt_copy_2d_async", "vrt_copy_to_device", "vrt_temporal_blend", "vrt_temporal_filter",
     "vrt_ipc_alloc_frame", "vrt_ipc_open", "vrt_ipc_close", "vrt_scene_fill", "vrt_noise_heightmap", "vrt_atlas_synthetic",
     "vrt_atlas_pack", "vrt_camera_invpv", "vrt_sun_dir", "vrt_write_png",
 ]
@@ -145,6 +145,7 @@ def _signatures():
         "vrt_copy_to_host": (i32, [vp, vp, vp, C.c_size_t, vp]),
         "vrt_copy_to_device": (i32, [vp, vp, vp, C.c_size_t, vp]),
         "vrt_copy_to_host_async": (i32, [vp, vp, vp, C.c_size_t, vp]),
+        "vrt_copy_2d_async": (i32, [vp, vp, C.c_size_t, vp, C.c_size_t, C.c_size_t, C.c_size_t, vp]),
         "vrt_temporal_blend": (i32, [vp, vp, vp, i64, f32, vp]),
         "vrt_temporal_filter": (i32, [vp, vp, vp, vp, i64, f32, vp]),
         "vrt_ipc_alloc_frame": (i32, [vp, C.c_size_t, C.POINTER(vp), vp]),
@@ -427,6 +428,9 @@ class Context:
     def copy_to_host_async(self, host_ptr, d_ptr, nbytes, stream=None):
         """Device -> (pinned) host, not synchronised; host_ptr from host_alloc()."""
         self._check(self.lib.vrt_copy_to_host_async(self.h, host_ptr, d_ptr, nbytes, stream))
+
+    def copy_2d_async(self, d_dst, dst_pitch, d_src, src_pitch, width_bytes, height, stream=None):
+        self._check(self.lib.vrt_copy_2d_async(self.h, d_dst, dst_pitch, d_src, src_pitch, width_bytes, height, stream))
 
     def copy_to_device(self, d_ptr, arr, stream=None):
         a = np.ascontiguousarray(arr)

@@ -653,6 +653,14 @@ int vrt_copy_to_host_async(vrt_ctx* ctx, void* host, const void* d_src, size_t b
   return VRT_OK;
 }
 
+int vrt_copy_2d_async(vrt_ctx* ctx, void* d_dst, size_t dst_pitch, const void* d_src, size_t src_pitch, size_t width_bytes, size_t height, void* stream) {
+  if (!ctx || !d_dst || !d_src) return fail(ctx, VRT_E_INVALID, "vrt_copy_2d_async: NULL argument");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(cudaMemcpy2DAsync(d_dst, dst_pitch, d_src, src_pitch, width_bytes, height, cudaMemcpyDefault, (cudaStream_t)stream));
+  return VRT_OK;
+}
+
 int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes, void* stream) {
   if (!ctx || !d_dst || !host) return fail(ctx, VRT_E_INVALID, "vrt_copy_to_device: NULL argument");
   int rc = bind(ctx);
