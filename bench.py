@@ -7,10 +7,12 @@
 A "step" is one 1920x1080 frame of the 128^3 terrain scene (BASELINE config 2: primary + shadow rays)
 per GPU; the recorded poses are cycled.  A "ray" is one RayMarch or RayMarchShadow invocation as the
 reference algorithm executes it (voxel.glsl:259,302), counted once per pose by the exact kernel's
-counters (tests prove they equal the oracle's).  N > 1: one process per GPU (torchrun), every rank renders
-its own pose's frame (weak scaling, grid replicated) and the frames are all-gathered over NCCL on a
-side stream, overlapped with the next step's render; time is the max over ranks.
-Prints ONE JSON line on rank 0.
+counters (tests prove they equal the oracle's).  N > 1: one process per GPU (torchrun), grid replicated.
+  --scaling weak (default): every rank renders its own pose's frame - independent units, no data-path collective in the timed
+      steps; a second pass measures the fused NVLink gather of ALL frames into rank 0 and reports it as `gathered`.
+  --scaling strong: ONE frame per step, 16-row bands dealt round-robin over the ranks, every rank's render kernel storing its
+      bands straight into rank 0's frame over NVLink (fused render + gather, CUDA IPC mapping).
+Time is the max over ranks.  Prints ONE JSON line on rank 0.
 """
 import argparse
 import ctypes as C
@@ -90,8 +92,9 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
-    ap.add_argument("--gather", default="p2p", choices=["p2p", "dma", "nccl", "none"],
-                    help="N>1: p2p = every rank's render kernel stores straight into rank 0's frame over NVLink (fused render+gather); "
+    ap.add_argument("--gather", default=None, choices=["p2p", "dma", "nccl", "none"],
+                    help="N>1 (default: p2p with --scaling strong, where the tiles of ONE frame have to meet; none with --scaling weak, where every GPU "
+                         "renders its own frames - the fused gather of all frames into rank 0 is then measured in a second pass and reported as `gathered`): p2p = every rank's render kernel stores straight into rank 0's frame over NVLink (fused render+gather); "
                          "dma = every rank renders into its own memory and a copy-engine transfer on a side stream puts the pixels into rank 0's frame "
                          "(overlaps the next frame's render when frames are pipelined); "
                          "nccl = all_gather_into_tensor after the render; none = frames stay on their GPUs")
@@ -308,11 +311,13 @@ def run_ours(args):
     if args.persistent:
         flags |= vrt.FLAG_PERSISTENT
     strong = args.scaling == "strong" and world > 1
-    gather = args.gather if world > 1 else "none"
+    gather = "none" if world == 1 else (args.gather or ("p2p" if strong else "none"))
+    also_gathered = world > 1 and not strong and gather == "none"                   # weak scaling: second pass with the fused gather
     BR = 16
     npix = W * H
     ipc = gather in ("p2p", "dma")                                                # rank 0 owns the gathered frames, the others map them
-    gbpp = 3 if (ipc and args.gather_format == "rgb8") else 4                       # bytes per pixel of the gathered frames
+    want_ipc = ipc or also_gathered
+    gbpp = 3 if (want_ipc and args.gather_format == "rgb8") else 4                  # bytes per pixel of the gathered frames
     frame_bytes = npix * gbpp
     if strong:      # ONE frame per step: every rank renders its 16-row bands of the same pose
         full = [mk(common, args.workload, W, H, sc, poses[i % len(poses)], flags) for i in range(len(poses))]
@@ -351,10 +356,10 @@ def run_ours(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")                        # > 126 MB L2
     token = torch.zeros(1, dtype=torch.int32, device="cuda")
     slots = 1 if strong else world                                                          # frames held by rank 0 per step
-    local_fb = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(2)]
+    local_fb = [torch.empty(npix * 4, dtype=torch.uint8, device="cuda") for _ in range(2)]
     gathered = None
     p2p_base = None
-    if ipc:
+    if want_ipc:
         # rank 0 owns the gathered frames (double-buffered); the others map them through CUDA IPC and store into them.
         # If the mapping fails on any rank (no peer access between the devices), every rank falls back to the NCCL gather.
         ok = 1
@@ -381,11 +386,11 @@ def run_ours(args):
         if int(flag.item()) == 1:
             p2p_base = int(p2p_base.value)
         else:
-            gather, p2p_base, ipc = "nccl", None, False
+            gather, p2p_base, ipc, want_ipc, also_gathered = ("nccl" if ipc else gather), None, False, False, False
     # What the gather can reach at best: every rank but 0 copies a frame-sized buffer into its slot of rank 0's memory, all at once
     # (plain device-to-peer copy kernels, no rendering): aggregate GB/s into rank 0 = the NVLink ingest ceiling of this box.
     ingest_peak_gbs = None
-    if ipc:
+    if want_ipc:
         reps = 20
         src = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
         dst = _wrap_device(torch, p2p_base + (rank if not strong else 0) * frame_bytes, frame_bytes) if rank != 0 else None
@@ -407,7 +412,7 @@ def run_ours(args):
 
     def target(i):
         """(params, device pointer) of step i's output for this rank."""
-        p = gframes[i % len(frames)]
+        p = gframes[i % len(frames)] if ipc else frames[i % len(frames)]
         if gather == "p2p":
             if strong:
                 q = p.copy()
@@ -592,6 +597,43 @@ def run_ours(args):
             dist.barrier()
         t_pipeline = p0.elapsed_time(p1) / 1e3
 
+    # Weak scaling, second pass: the same K steps with every rank's render kernel storing its frame straight into rank 0's memory over
+    # NVLink (the fused render + gather of the tile-sharded mode applied to whole frames): what collecting ALL frames on one GPU costs.
+    gathered_pass = None
+    if also_gathered:
+        gev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        torch.cuda.synchronize(); dist.barrier()
+        for i in range(-3, args.steps):
+            with torch.cuda.stream(stream):
+                flush.fill_(i & 0xFF)
+                if i >= 0:
+                    gev[i][0].record(stream)
+                ctx.render_to(gframes[i % len(frames)], p2p_base + ((i % 2) * world + rank) * frame_bytes, stream.cuda_stream)
+                if i >= 0:
+                    gev[i][1].record(stream)
+                rendered = torch.cuda.Event(); rendered.record(stream)
+            with torch.cuda.stream(comm):
+                comm.wait_event(rendered)
+                dist.all_reduce(token)               # "all stores of this step have landed"
+                done = torch.cuda.Event(); done.record(comm)
+            stream.wait_event(done)
+        torch.cuda.synchronize(); dist.barrier()
+        tg = torch.tensor([sum(a.elapsed_time(b) for a, b in gev) / 1e3], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tg, op=dist.ReduceOp.MAX)
+        # check: rank 0 holds every rank's last frame (sums, like gather_check)
+        loc = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
+        last = args.steps - 1
+        ctx.render_to(gframes[last % len(frames)], loc.data_ptr(), None); torch.cuda.synchronize()
+        mine = loc.to(torch.int64).sum().reshape(1)
+        sums = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(sums, mine)
+        ok = None
+        if rank == 0:
+            held = _wrap_device(torch, p2p_base + (last % 2) * world * frame_bytes, world * frame_bytes)
+            ok = all(int(held[r * frame_bytes:(r + 1) * frame_bytes].to(torch.int64).sum()) == int(sums[r]) for r in range(world))
+        gathered_pass = {"t": float(tg.item()), "ok": ok}
+        dist.barrier()
+
     # e2e through the host-facing API, every step: params by value in (h2d), this rank's pixels back in pinned host memory (d2h).
     #  sync form : vrt_render_host - render, copy, synchronise, one frame at a time
     #  overlapped: vrt_render_to + vrt_copy_to_host_async on two streams with two device/host buffers (two frames in flight), the
@@ -706,12 +748,14 @@ def run_ours(args):
         ach_issue = instr_per_launch / per_launch_s
         frames_total = args.steps * (1 if strong else world)
         shard = "one GPU" if world == 1 else (
-            ("ONE frame per step split into 16-row bands dealt round-robin over the ranks" if strong else "one frame per GPU per step (pose batch)")
+            ("ONE frame per step split into 16-row bands dealt round-robin over the ranks" if strong else
+             "one frame per GPU per step (pose batch): independent units, no data-path collective - every frame stays in (and, in the e2e leg, goes to the host from) the GPU that rendered it")
             + ", grid replicated; gather: " + {"p2p": "every rank's render kernel stores its pixels straight into rank 0's frame over NVLink (CUDA IPC mapping), "
                                                       "4-byte NCCL all-reduce per step as the completion signal (overlapped)",
                                                "dma": "every rank renders into its own memory; a copy-engine transfer on a side stream (cudaMemcpy2DAsync into rank 0's frame, CUDA IPC mapping) "
                                                       "follows inside the step window and overlaps the next frame's render in the pipelined pass",
-                                               "nccl": "all_gather_into_tensor after the render, inside the step window", "none": "none"}[gather])
+                                               "nccl": "all_gather_into_tensor after the render, inside the step window",
+                                               "none": "none in the timed steps; the fused NVLink gather of all frames into rank 0 is measured in a second pass (`gathered`)"}[gather])
         # What the timed kernel really executes, from the committed ncu capture of this workload at 1 GPU (per-launch means over the
         # cycled poses); the TIME it is divided by is this run's own CUDA-event time.  Only meaningful when the launches are the
         # captured ones: one GPU, full frames, default traversal.
@@ -774,6 +818,12 @@ def run_ours(args):
                     "frac_of_d2h_bound": t_copy / t_e2e if world == 1 else None},
             "gpu_launches": int(launches_timed),      # render_kernel launches of rank 0 inside the timed region (one per step)
             "gather_check": gather_check,
+            "gathered": None if not gathered_pass else {
+                "value": rays_all / gathered_pass["t"] / 1e6, "unit": "Mrays/s", "ms_per_step": 1e3 * gathered_pass["t"] / args.steps,
+                "what": "second pass of the same K steps: every rank's render kernel stores its frame straight into rank 0's memory over NVLink (fused "
+                        "render + gather, %s), 4-byte NCCL all-reduce per step as the completion signal; bound by what ONE GPU can ingest" % ("packed RGB8" if gbpp == 3 else "RGBA8"),
+                "bytes_into_rank0_per_step": (world - 1) * frame_bytes, "achieved_gbs": (world - 1) * frame_bytes * args.steps / gathered_pass["t"] / 1e9,
+                "ingest_peak_gbs": ingest_peak_gbs, "check": "ok" if gathered_pass["ok"] else "MISMATCH"},
             "gather": None if not ipc else {
                 "how": "render kernel's own stores (fused)" if gather == "p2p" else "copy engines after a render into local memory (dma)",
                 "format": "packed RGB8 (the reference's colour attachment format)" if gbpp == 3 else "RGBA8",
