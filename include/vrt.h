@@ -195,6 +195,20 @@ int vrt_read_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count); /* count m
  * touch while it travels k cells along the dominant axis of the direction). */
 int vrt_read_sun_cells(vrt_ctx* ctx, uint16_t* host_cells, size_t count);
 
+/* ---- repack without allocation ----
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  Builds the ISOTROPIC traversal cells (the octants == 1 layout
+ * above: (size+2)^3 uint16, radius cap 255 or VRT_OPT_RADIUS_CAP) of a chunk that is already in device memory into caller-provided
+ * device memory, asynchronously on `stream`.  The scratch of the distance transform (2 x size^3 bytes) lives in a fixed device array
+ * inside the library - 4 MiB per GPU that loads libvrt.so, held until the process exits - so size is limited to
+ * VRT_REPACK_STATIC_MAX_SIZE; larger sizes are rejected with VRT_E_INVALID.  The call allocates and frees nothing and does not touch the
+ * ctx's own grid (vrt_upload_grid is still what a render needs).  All calls share the one scratch array, which keeps the last call's
+ * contents (every pass overwrites what it later reads, nothing needs clearing): calls that overlap on the GPU - different streams,
+ * different contexts of one device - race on it and must be serialised by the caller.
+ *   d_voxels: size^3 bytes, x + y*size + z*size*size;  d_cells: (size+2)^3 uint16, written completely. */
+#define VRT_REPACK_STATIC_MAX_SIZE 128
+int vrt_repack_static(vrt_ctx* ctx, const void* d_voxels, int size, void* d_cells, void* stream);
+
 /* Tuning options; 1 and 2 take effect at the next vrt_upload_grid, 3 and 4 at the next render. */
 enum {
   VRT_OPT_OCTANT_FIELDS = 1, /* 1 (default) = eight direction-octant radius fields, 0 = one isotropic field */

@@ -19,6 +19,7 @@ OPT_OCTANT_FIELDS = 1
 OPT_RADIUS_CAP = 2
 OPT_HOST_DIRECT = 3
 OPT_SUN_FIELD = 4
+REPACK_STATIC_MAX_SIZE = 128
 HIT_MISS = 0xFFFFFFFF
 
 SCENE_TERRAIN, SCENE_GLASS_CUBE, SCENE_REFRACTION, SCENE_SYNTHETIC = 0, 1, 2, 3
@@ -28,7 +29,7 @@ EXPORTS = [
     "vrt_default_params", "vrt_abi_version", "vrt_create", "vrt_destroy", "vrt_last_error", "vrt_last_warning", "vrt_device_memset", "vrt_upload_grid",
     "vrt_upload_grid_device", "vrt_upload_atlas", "vrt_render", "vrt_render_to", "vrt_render_host", "vrt_tile_pixels", "vrt_probe_read_gbs",
     "vrt_framebuffer_device", "vrt_read_framebuffer", "vrt_read_debug_maps", "vrt_read_float_frame", "vrt_reset_counters",
-    "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells", "vrt_read_sun_cells", "vrt_set_option",
+    "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells", "vrt_read_sun_cells", "vrt_repack_static", "vrt_set_option",
     "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_host_async", "vrt_copy_2d_async", "vrt_copy_to_device", "vrt_temporal_blend", "vrt_temporal_filter",
     "vrt_ipc_alloc_frame", "vrt_ipc_open", "vrt_ipc_close", "vrt_scene_fill", "vrt_noise_heightmap", "vrt_atlas_synthetic",
     "vrt_atlas_pack", "vrt_camera_invpv", "vrt_sun_dir", "vrt_write_png",
@@ -136,6 +137,7 @@ def _signatures():
         "vrt_grid_info_get": (i32, [vp, C.POINTER(GridInfo)]),
         "vrt_read_cells": (i32, [vp, vp, C.c_size_t]),
         "vrt_read_sun_cells": (i32, [vp, vp, C.c_size_t]),
+        "vrt_repack_static": (i32, [vp, vp, i32, vp, vp]),
         "vrt_set_option": (i32, [vp, i32, i32]),
         "vrt_host_alloc": (i32, [vp, C.c_size_t, C.POINTER(vp)]),
         "vrt_host_free": (i32, [vp, vp]),
@@ -387,6 +389,10 @@ class Context:
         out = np.zeros(self.grid_info().cells_total, np.uint16)
         self._check(self.lib.vrt_read_cells(self.h, _ptr(out), out.size))
         return out
+
+    def repack_static(self, d_voxels, size, d_cells, stream=None):
+        """vrt_repack_static: isotropic cells of a device-resident chunk into caller memory, no allocation (size <= 128)."""
+        self._check(self.lib.vrt_repack_static(self.h, d_voxels, size, d_cells, stream))
 
     def read_sun_cells(self):
         out = np.zeros((self.grid_info().size + 2) ** 3, np.uint16)

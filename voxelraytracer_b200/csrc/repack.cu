@@ -182,6 +182,29 @@ cudaError_t launch_repack(const uint8_t* d_grid, int n, int radius_cap, uint8_t*
   return cudaGetLastError();
 }
 
+// ---- repack without any allocation (vrt_repack_static; no counterpart in the reference) ----
+// The two n^3-byte scratch volumes of the isotropic repack live in a file-scope device array instead of a cudaMalloc'ed buffer, for
+// callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid it).  2 x 128^3 bytes = 4 MiB, held by
+// every GPU that loads the library until the process exits.  In HOST code `g_repack_scratch` is only a stand-in for the symbol, not a
+// device address: the address is looked up once per device with cudaGetSymbolAddress (that device current) and passed to the kernels.
+// Every call shares the array and it keeps the last call's contents; each pass overwrites all n^3 bytes it later reads, so nothing has
+// to start at zero - but two calls that overlap on the GPU (different streams) race on it.
+static __device__ __align__(256) uint8_t g_repack_scratch[2u * VRT_REPACK_STATIC_MAX_SIZE * VRT_REPACK_STATIC_MAX_SIZE * VRT_REPACK_STATIC_MAX_SIZE];
+
+cudaError_t launch_repack_static(const uint8_t* d_grid, int n, int radius_cap, uint16_t* d_cells, int device, cudaStream_t stream, int* launches) {
+  constexpr int kMaxDevices = 64;
+  static uint8_t* scratch_of[kMaxDevices] = {nullptr};     // device address of g_repack_scratch on each device, looked up on first use
+  if (device < 0 || device >= kMaxDevices || n < 1 || n > VRT_REPACK_STATIC_MAX_SIZE) return cudaErrorInvalidValue;
+  if (!scratch_of[device]) {
+    uint8_t* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_repack_scratch);   // the caller has made `device` current
+    if (e != cudaSuccess) return e;
+    scratch_of[device] = ptr;
+  }
+  uint8_t* tmp = scratch_of[device];
+  return launch_repack(d_grid, n, radius_cap, tmp, tmp + (size_t)n * n * n, d_cells, nullptr, stream, launches);
+}
+
 // Eight octant arrays, d_cells + o * (n+2)^3 for o = (sx < 0) | (sy < 0) << 1 | (sz < 0) << 2.  The x pass is shared by
 // the four octants with the same sx, the y pass by the two with the same (sx, sy): 2 + 4 + 8 passes + 8 packs.
 // tmp_a: n^3 bytes (x pass), tmp_b: n^3 (y pass), tmp_c: n^3 (z pass).

@@ -519,6 +519,21 @@ int vrt_read_sun_cells(vrt_ctx* ctx, uint16_t* host, size_t count) {
   return VRT_OK;
 }
 
+int vrt_repack_static(vrt_ctx* ctx, const void* d_voxels, int size, void* d_cells, void* stream) {
+  if (!ctx || !d_voxels || !d_cells) return fail(ctx, VRT_E_INVALID, "vrt_repack_static: NULL argument");
+  if (size < 8 || (size & (size - 1)) != 0) return fail(ctx, VRT_E_INVALID, "vrt_repack_static: grid size %d must be a power of two >= 8", size);
+  if (size > VRT_REPACK_STATIC_MAX_SIZE)
+    return fail(ctx, VRT_E_INVALID, "vrt_repack_static: grid size %d exceeds VRT_REPACK_STATIC_MAX_SIZE = %d (the fixed scratch array holds 2 x %d^3 bytes); "
+                "use vrt_upload_grid for larger chunks", size, VRT_REPACK_STATIC_MAX_SIZE, VRT_REPACK_STATIC_MAX_SIZE);
+  int rc = bind(ctx);                                      // makes ctx->device current: the scratch address is per device
+  if (rc) return rc;
+  const int cap = ctx->opt_radius_cap > 0 ? ctx->opt_radius_cap : 255;
+  int launches = 0;
+  CU(launch_repack_static((const uint8_t*)d_voxels, size, cap, (uint16_t*)d_cells, ctx->device, (cudaStream_t)stream, &launches));
+  ctx->launches += launches;
+  return VRT_OK;
+}
+
 int vrt_set_option(vrt_ctx* ctx, int option, int value) {
   if (!ctx) return fail(ctx, VRT_E_INVALID, "vrt_set_option: NULL ctx");
   switch (option) {

@@ -19,6 +19,10 @@ cudaError_t launch_render_persistent(const FrameArgs& args, bool flat, bool glas
 cudaError_t launch_repack(const uint8_t* d_grid, int n, int radius_cap, uint8_t* tmp_a, uint8_t* tmp_b, uint16_t* d_cells,
                           unsigned long long* d_stats, cudaStream_t stream, int* launches);
 
+// The same isotropic repack with its scratch in a file-scope device array of repack.cu (no allocation; n <= VRT_REPACK_STATIC_MAX_SIZE).
+// `device` must be the current device.
+cudaError_t launch_repack_static(const uint8_t* d_grid, int n, int radius_cap, uint16_t* d_cells, int device, cudaStream_t stream, int* launches);
+
 // Octant fields: 8 arrays of (n+2)^3 cells at d_cells (see repack.cu).  tmp_a/b/c: n^3 bytes each.
 cudaError_t launch_repack_octants(const uint8_t* d_grid, int n, int radius_cap, uint8_t* tmp_a, uint8_t* tmp_b, uint8_t* tmp_c,
                                   uint16_t* d_cells, unsigned long long* d_stats, cudaStream_t stream, int* launches);
