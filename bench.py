@@ -108,6 +108,7 @@ def parse():
     ap.add_argument("--radius-cap", type=int, default=0, help="VRT_OPT_RADIUS_CAP (tuning comparison; 0 = default)")
     ap.add_argument("--no-affinity", action="store_true", help="N > 1: do not restrict each rank to its GPU's local host cores")
     ap.add_argument("--e2e-depth", type=int, default=4, help="frames in flight in the overlapped e2e leg")
+    ap.add_argument("--remote-rows", type=int, default=1, choices=[0, 1], help="VRT_OPT_REMOTE_ROWS (tuning comparison; 1 = default)")
     ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
     return ap.parse_args()
 
@@ -302,6 +303,7 @@ def run_ours(args):
     ctx = vrt.Context(local)
     ctx.set_option(vrt.OPT_OCTANT_FIELDS, args.octants)
     ctx.set_option(vrt.OPT_RADIUS_CAP, args.radius_cap)
+    ctx.set_option(vrt.OPT_REMOTE_ROWS, args.remote_rows)
     t_up0 = time.perf_counter()
     ctx.upload_grid(grid, n)
     t_upload = time.perf_counter() - t_up0
@@ -540,6 +542,20 @@ def run_ours(args):
         t_kernel = sum(a.elapsed_time(b) for a, b in kev) / 1e3
     else:
         t_kernel = t_steps
+    # The kernel's own duration, for the roofline: the same K steps (same L2 flush before each), each read back through the library's
+    # event pair, which is recorded directly around the launch on the launching stream (vrt_last_render_ms); the step windows above also
+    # hold torch's event records and the gap between them and the launch.
+    kms = []
+    for i in range(args.steps):
+        p, ptr = target(i)
+        with torch.cuda.stream(stream):
+            flush.fill_(i & 0xFF)
+            ctx.render_to(p, ptr, stream.cuda_stream)
+        kms.append(ctx.last_render_ms())
+    t_kernel = sum(kms) / 1e3
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
     clocks = sampler.stop(m0, m1) if rank == 0 else None
     rays = sum(counts[i % len(frames)]["rays"] for i in range(args.steps))
     steps_ref = sum(counts[i % len(frames)]["steps"] for i in range(args.steps))
@@ -786,7 +802,8 @@ def run_ours(args):
                     "host_affinity": None if world == 1 else ("rank 0 on the %d host cores local to its GPU (NVML), likewise every rank" % host_cores
                                                               if host_cores else "not set")},
             "frames_per_s": frames_total / t_step_total,
-            "kernel_ms_per_launch": 1e3 * t_kernel_max / args.steps,
+            "kernel_ms_per_launch": 1e3 * t_kernel_max / args.steps, "kernel_ms_per_launch_median": float(np.median(kms)), "kernel_ms_per_launch_min": float(np.min(kms)),
+            "kernel_ms_def": "render kernel only: the library's CUDA-event pair around the launch on the launching stream (vrt_last_render_ms), separate pass of the same K steps, L2 flushed before each",
             "rays_per_frame": rays_all / frames_total, "ref_steps_per_frame": steps_all / frames_total,
             "actual_steps_per_frame": act_all / frames_total,
             "gsteps_per_s": steps_all / t_step_total / 1e9,

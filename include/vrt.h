@@ -218,6 +218,9 @@ enum {
                                 the second consecutive frame with the same u_SunDir - ~0.3 ms at 128^3 - so a sun that moves every frame, the
                                 reference's day / night cycle, never pays for it); 2 = for every chunk size, rebuilt at once whenever u_SunDir
                                 changes; 0 = shadow rays walk the sun's octant field.  Same pixels in every mode. */
+  VRT_OPT_REMOTE_ROWS = 5,   /* 1 (default) = a colour target outside this GPU's memory (peer / IPC mapping, pinned host memory) is written by the 32x4-pixel CTA
+                                arrangement whose warps store whole 128-byte rows (what a bandwidth-bound link wants); 0 = by the same 16x8 arrangement with
+                                per-thread stores as local frames (no shared-memory stage, no CTA barrier: what a latency-bound small tile wants) */
   VRT_OPT_HOST_DIRECT = 3    /* 1 (default) = vrt_render_host into PINNED host memory lets the render kernel store the pixels straight
                                 into it over PCIe (no device frame, no copy); 0 = always render to the device frame, then copy */
 };

@@ -22,6 +22,7 @@ from .api import (  # noqa: F401
     OPT_OCTANT_FIELDS,
     OPT_RADIUS_CAP,
     OPT_HOST_DIRECT,
+    OPT_REMOTE_ROWS,
     OPT_SUN_FIELD,
     Context,
     Counters,

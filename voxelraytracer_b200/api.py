@@ -19,6 +19,7 @@ OPT_OCTANT_FIELDS = 1
 OPT_RADIUS_CAP = 2
 OPT_HOST_DIRECT = 3
 OPT_SUN_FIELD = 4
+OPT_REMOTE_ROWS = 5
 REPACK_STATIC_MAX_SIZE = 128
 HIT_MISS = 0xFFFFFFFF
 

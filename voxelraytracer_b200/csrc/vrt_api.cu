@@ -29,6 +29,7 @@ struct vrt_ctx {
   int octants = 0;                 // what d_cells holds
   int opt_radius_cap = 0;          // VRT_OPT_RADIUS_CAP, 0 = default by chunk size
   int opt_host_direct = 1;         // VRT_OPT_HOST_DIRECT
+  int opt_remote_rows = 1;         // VRT_OPT_REMOTE_ROWS: remote targets get the 32x4 CTA arrangement that stores whole 128-byte rows
   int opt_sun_field = 1;           // VRT_OPT_SUN_FIELD: 0 off, 1 auto (chunks up to 256^3, once the sun direction repeats), 2 always
   float sun_seen[3] = {0, 0, 0};   // sun direction of the previous render (auto mode builds on the second frame in a row with the same one)
   uint16_t* d_sun = nullptr;       // the sun field (one more (n+2)^3 array), valid for sun_dir / sun_base
@@ -377,7 +378,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   if ((p->flags & VRT_FLAG_PERSISTENT) && !debug && !(p->flags & (VRT_FLAG_EXACT | VRT_FLAG_RGB8_OUT))) {
     CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, ctx->info.voxels_glass != 0, ctx->d_tickets + tm, ctx->num_sms, s));
   } else {
-    CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, remote_target(ctx, d_out), ctx->info.voxels_glass != 0, s));
+    CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, ctx->opt_remote_rows && remote_target(ctx, d_out), ctx->info.voxels_glass != 0, s));
   }
   CU(cudaEventRecord(ctx->ev1[tm], s));
   ctx->launches += 1;
@@ -539,6 +540,7 @@ int vrt_set_option(vrt_ctx* ctx, int option, int value) {
   switch (option) {
     case VRT_OPT_OCTANT_FIELDS: ctx->opt_octants = value ? 1 : 0; return VRT_OK;
     case VRT_OPT_HOST_DIRECT: ctx->opt_host_direct = value ? 1 : 0; return VRT_OK;
+    case VRT_OPT_REMOTE_ROWS: ctx->opt_remote_rows = value ? 1 : 0; return VRT_OK;
     case VRT_OPT_SUN_FIELD:
       if (value < 0 || value > 2) return fail(ctx, VRT_E_INVALID, "vrt_set_option: sun field mode %d not in [0,2]", value);
       ctx->opt_sun_field = value; return VRT_OK;
