@@ -108,6 +108,7 @@ def parse():
     ap.add_argument("--radius-cap", type=int, default=0, help="VRT_OPT_RADIUS_CAP (tuning comparison; 0 = default)")
     ap.add_argument("--no-affinity", action="store_true", help="N > 1: do not restrict each rank to its GPU's local host cores")
     ap.add_argument("--e2e-depth", type=int, default=4, help="frames in flight in the overlapped e2e leg")
+    ap.add_argument("--pipe-depth", type=int, default=4, help="frames in flight in the `pipelined` pass (and number of gather target buffers)")
     ap.add_argument("--remote-rows", type=int, default=1, choices=[0, 1], help="VRT_OPT_REMOTE_ROWS (tuning comparison; 1 = default)")
     ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
     return ap.parse_args()
@@ -316,6 +317,7 @@ def run_ours(args):
     gather = "none" if world == 1 else (args.gather or ("p2p" if strong else "none"))
     also_gathered = world > 1 and not strong and gather == "none"                   # weak scaling: second pass with the fused gather
     BR = 16
+    NBUF = max(2, args.pipe_depth)                                                   # target buffers (frames that may be in flight)
     npix = W * H
     ipc = gather in ("p2p", "dma")                                                # rank 0 owns the gathered frames, the others map them
     want_ipc = ipc or also_gathered
@@ -358,7 +360,7 @@ def run_ours(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")                        # > 126 MB L2
     token = torch.zeros(1, dtype=torch.int32, device="cuda")
     slots = 1 if strong else world                                                          # frames held by rank 0 per step
-    local_fb = [torch.empty(npix * 4, dtype=torch.uint8, device="cuda") for _ in range(2)]
+    local_fb = [torch.empty(npix * 4, dtype=torch.uint8, device="cuda") for _ in range(NBUF)]
     gathered = None
     p2p_base = None
     if want_ipc:
@@ -367,7 +369,7 @@ def run_ours(args):
         ok = 1
         try:
             if rank == 0:
-                p2p_base, handle = ctx.ipc_alloc_frame(2 * slots * frame_bytes)
+                p2p_base, handle = ctx.ipc_alloc_frame(NBUF * slots * frame_bytes)
                 box = [handle]
             else:
                 box = [None]
@@ -410,7 +412,7 @@ def run_ours(args):
     if gather == "nccl":
         per = sharding.max_rows(H, world, BR) * W * 4 if strong else frame_bytes          # nccl gather: always RGBA8
         gathered = torch.empty(world * per, dtype=torch.uint8, device="cuda")
-        local_fb = [torch.zeros(per, dtype=torch.uint8, device="cuda") for _ in range(2)]
+        local_fb = [torch.zeros(per, dtype=torch.uint8, device="cuda") for _ in range(NBUF)]
 
     def target(i):
         """(params, device pointer) of step i's output for this rank."""
@@ -419,24 +421,24 @@ def run_ours(args):
             if strong:
                 q = p.copy()
                 q.flags |= vrt.FLAG_OUT_FRAME          # bands land at their frame rows inside rank 0's frame
-                return q, p2p_base + (i % 2) * frame_bytes
-            return p, p2p_base + ((i % 2) * world + rank) * frame_bytes
-        return p, local_fb[i % 2].data_ptr()
+                return q, p2p_base + (i % NBUF) * frame_bytes
+            return p, p2p_base + ((i % NBUF) * world + rank) * frame_bytes
+        return p, local_fb[i % NBUF].data_ptr()
 
     def dma_gather(i, st):
         """gather == dma: this rank's pixels of step i, rendered compactly into local_fb, go to rank 0's frame through the copy engines."""
-        src = local_fb[i % 2].data_ptr()
+        src = local_fb[i % NBUF].data_ptr()
         if strong:
             chunk = BR * W * gbpp                                      # one band of rows, contiguous on both sides
             rows_mine = my_pix // W
             nb, tail = rows_mine // BR, rows_mine % BR
-            dst = p2p_base + (i % 2) * frame_bytes + rank * chunk
+            dst = p2p_base + (i % NBUF) * frame_bytes + rank * chunk
             if nb:
                 ctx.copy_2d_async(dst, world * chunk, src, chunk, chunk, nb, st.cuda_stream)
             if tail:                                                    # a last, shorter band
                 ctx.copy_2d_async(dst + nb * world * chunk, world * chunk, src + nb * chunk, chunk, tail * W * gbpp, 1, st.cuda_stream)
         else:
-            ctx.copy_2d_async(p2p_base + ((i % 2) * world + rank) * frame_bytes, frame_bytes, src, frame_bytes, frame_bytes, 1, st.cuda_stream)
+            ctx.copy_2d_async(p2p_base + ((i % NBUF) * world + rank) * frame_bytes, frame_bytes, src, frame_bytes, frame_bytes, 1, st.cuda_stream)
 
     def one_step(i, ev0=None, ev1=None, do_flush=True):
         """flush (untimed) -> [ev0] render (p2p: its stores ARE the gather) (+ nccl gather) [ev1].  Returns the completion event."""
@@ -458,7 +460,7 @@ def run_ours(args):
         with torch.cuda.stream(comm):
             comm.wait_event(rendered)
             if gather == "nccl":
-                dist.all_gather_into_tensor(gathered, local_fb[i % 2])
+                dist.all_gather_into_tensor(gathered, local_fb[i % NBUF])
                 if ev1 is not None:
                     ev1.record(comm)
             elif gather == "dma":
@@ -570,15 +572,15 @@ def run_ours(args):
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
-        streams2 = [stream, torch.cuda.Stream()]
-        last = [None, None]
+        streams2 = [stream] + [torch.cuda.Stream() for _ in range(NBUF - 1)]
+        last = [None] * NBUF
 
         def pipe_step(i):
             p, ptr = target(i)
-            st = streams2[i % 2]
+            st = streams2[i % NBUF]
             with torch.cuda.stream(st):
-                if last[i % 2] is not None:
-                    st.wait_event(last[i % 2])           # buffer i%2 is free once step i-2 (and its gather) finished
+                if last[i % NBUF] is not None:
+                    st.wait_event(last[i % NBUF])        # buffer i % NBUF is free once step i - NBUF (and its gather) finished
                 ctx.render_to(p, ptr, st.cuda_stream)
                 rendered = torch.cuda.Event(); rendered.record(st)
             done = rendered
@@ -586,27 +588,28 @@ def run_ours(args):
                 with torch.cuda.stream(comm):
                     comm.wait_event(rendered)
                     if gather == "nccl":
-                        dist.all_gather_into_tensor(gathered, local_fb[i % 2])
+                        dist.all_gather_into_tensor(gathered, local_fb[i % NBUF])
                     elif gather == "dma":
                         dma_gather(i, comm)
                         dist.all_reduce(token)
                     else:
                         dist.all_reduce(token)
                     done = torch.cuda.Event(); done.record(comm)
-            last[i % 2] = done
+            last[i % NBUF] = done
 
-        for i in range(4):
+        for i in range(2 * NBUF):
             pipe_step(i)
         torch.cuda.synchronize()
         p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        streams2[1].wait_stream(stream)
         p0.record(stream)
-        streams2[1].wait_event(p0)
+        for st_ in streams2[1:]:
+            st_.wait_event(p0)
         for i in range(args.steps):
             pipe_step(i)
         for e in last:
             stream.wait_event(e)
-        stream.wait_stream(streams2[1])
+        for st_ in streams2[1:]:
+            stream.wait_stream(st_)
         p1.record(stream)
         torch.cuda.synchronize()
         if world > 1:
@@ -624,7 +627,7 @@ def run_ours(args):
                 flush.fill_(i & 0xFF)
                 if i >= 0:
                     gev[i][0].record(stream)
-                ctx.render_to(gframes[i % len(frames)], p2p_base + ((i % 2) * world + rank) * frame_bytes, stream.cuda_stream)
+                ctx.render_to(gframes[i % len(frames)], p2p_base + ((i % NBUF) * world + rank) * frame_bytes, stream.cuda_stream)
                 if i >= 0:
                     gev[i][1].record(stream)
                 rendered = torch.cuda.Event(); rendered.record(stream)
@@ -645,7 +648,7 @@ def run_ours(args):
         dist.all_gather(sums, mine)
         ok = None
         if rank == 0:
-            held = _wrap_device(torch, p2p_base + (last % 2) * world * frame_bytes, world * frame_bytes)
+            held = _wrap_device(torch, p2p_base + (last % NBUF) * world * frame_bytes, world * frame_bytes)
             ok = all(int(held[r * frame_bytes:(r + 1) * frame_bytes].to(torch.int64).sum()) == int(sums[r]) for r in range(world))
         gathered_pass = {"t": float(tg.item()), "ok": ok}
         dist.barrier()
@@ -852,7 +855,7 @@ def run_ours(args):
             "upload_grid_s": t_upload, "radius_fields": "8 direction-octant fields" if args.octants else "1 isotropic field",
             "pipelined": None if not t_pipeline else {"value": rays_all / t_pipeline / 1e6, "unit": "Mrays/s",
                                                        "frames_per_s": frames_total / t_pipeline,
-                                                       "note": "two frames in flight on two streams, no L2 fills, one event pair around all K steps"},
+                                                       "note": "%d frames in flight on %d streams (as many target buffers), no L2 fills, one event pair around all K steps" % (NBUF, NBUF)},
             "clocks": clocks,
             "wall_s": t_wall,
         }

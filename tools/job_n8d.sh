@@ -1,0 +1,14 @@
+#!/bin/bash
+TR="timeout 280 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29518"
+$TR bench.py --gpus 8 --steps 120 --warmup 10 --workload c4 --scaling strong --pipe-depth 4 > gpurun_out/r02_bench_n8_c4s_d4.json 2> gpurun_out/r02_bench_n8_c4s_d4.err; echo rc=$?
+$TR bench.py --gpus 8 --steps 120 --warmup 10 --workload c4 --scaling strong --pipe-depth 8 > gpurun_out/r02_bench_n8_c4s_d8.json 2> gpurun_out/r02_bench_n8_c4s_d8.err; echo rc=$?
+python - <<'PY'
+import json
+for f in ("r02_bench_n8_c4s_d4", "r02_bench_n8_c4s_d8"):
+    try:
+        d = json.load(open("gpurun_out/%s.json" % f)); g = d.get("gather") or {}
+        print(f, "value %.0f ms %.4f kernel %.4f | pipelined %.0f = %.4f ms per frame (%s) | gather %.0f GB/s pipelined %.0f | check %s" % (
+            d["value"], d["ms_per_step"], d["kernel_ms_per_launch"], d["pipelined"]["value"], 1e3 / d["pipelined"]["frames_per_s"], d["pipelined"]["note"][:40], g.get("achieved_gbs") or 0, g.get("pipelined_gbs") or 0, d["gather_check"]))
+    except Exception as e:
+        print(f, "FAILED", e); print(open("gpurun_out/%s.err" % f).read()[-1500:])
+PY
