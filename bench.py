@@ -108,6 +108,9 @@ def parse():
     ap.add_argument("--radius-cap", type=int, default=0, help="VRT_OPT_RADIUS_CAP (tuning comparison; 0 = default)")
     ap.add_argument("--no-affinity", action="store_true", help="N > 1: do not restrict each rank to its GPU's local host cores")
     ap.add_argument("--e2e-depth", type=int, default=4, help="frames in flight in the overlapped e2e leg")
+    ap.add_argument("--signal", default="flag", choices=["flag", "nccl"],
+                    help="N>1, p2p gather: how rank 0 learns that a frame is complete - flag = every rank's stream adds to a counter in rank 0's memory after its "
+                         "render (vrt_signal_add) and rank 0's stream waits on it (vrt_stream_wait_value): no collective, no host round trip; nccl = 4-byte all-reduce per step")
     ap.add_argument("--pipe-depth", type=int, default=4, help="frames in flight in the `pipelined` pass (and number of gather target buffers)")
     ap.add_argument("--remote-rows", type=int, default=1, choices=[0, 1], help="VRT_OPT_REMOTE_ROWS (tuning comparison; 1 = default)")
     ap.add_argument("--persistent", action="store_true", help="VRT_FLAG_PERSISTENT launch (tuning comparison)")
@@ -369,7 +372,7 @@ def run_ours(args):
         ok = 1
         try:
             if rank == 0:
-                p2p_base, handle = ctx.ipc_alloc_frame(NBUF * slots * frame_bytes)
+                p2p_base, handle = ctx.ipc_alloc_frame(NBUF * slots * frame_bytes + 8192)
                 box = [handle]
             else:
                 box = [None]
@@ -389,6 +392,10 @@ def run_ours(args):
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         if int(flag.item()) == 1:
             p2p_base = int(p2p_base.value)
+            cnt_base = p2p_base + ((NBUF * slots * frame_bytes + 4095) // 4096) * 4096      # completion counters, one per target buffer
+            if rank == 0:
+                ctx.device_memset(cnt_base, 0, 4096); ctx.synchronize()
+            dist.barrier()
         else:
             gather, p2p_base, ipc, want_ipc, also_gathered = ("nccl" if ipc else gather), None, False, False, False
     # What the gather can reach at best: every rank but 0 copies a frame-sized buffer into its slot of rank 0's memory, all at once
@@ -425,6 +432,29 @@ def run_ours(args):
             return p, p2p_base + ((i % NBUF) * world + rank) * frame_bytes
         return p, local_fb[i % NBUF].data_ptr()
 
+    uses = [0] * NBUF
+    sig_flag = args.signal == "flag"
+
+    def completion(i, st_render, rendered):
+        """p2p gather: what tells rank 0 that every rank's stores of step i have landed.  Returns the event a consumer would wait on."""
+        slot = i % NBUF
+        uses[slot] += 1
+        done = torch.cuda.Event()
+        if sig_flag:
+            ctx.signal_add(cnt_base + 4 * slot, 1, st_render.cuda_stream)           # after this rank's render, on its stream
+            if rank == 0:
+                comm.wait_event(rendered)
+                ctx.stream_wait_value(cnt_base + 4 * slot, uses[slot] * world, comm.cuda_stream)
+                done.record(comm)
+            else:
+                done.record(st_render)
+        else:
+            with torch.cuda.stream(comm):
+                comm.wait_event(rendered)
+                dist.all_reduce(token)               # 4-byte all-reduce on the side stream
+                done.record(comm)
+        return done
+
     def dma_gather(i, st):
         """gather == dma: this rank's pixels of step i, rendered compactly into local_fb, go to rank 0's frame through the copy engines."""
         src = local_fb[i % NBUF].data_ptr()
@@ -457,6 +487,8 @@ def run_ours(args):
             return done
         rendered = torch.cuda.Event()
         rendered.record(stream)
+        if gather == "p2p":
+            return completion(i, stream, rendered)
         with torch.cuda.stream(comm):
             comm.wait_event(rendered)
             if gather == "nccl":
@@ -584,7 +616,9 @@ def run_ours(args):
                 ctx.render_to(p, ptr, st.cuda_stream)
                 rendered = torch.cuda.Event(); rendered.record(st)
             done = rendered
-            if gather != "none":
+            if gather == "p2p":
+                done = completion(i, st, rendered)
+            elif gather != "none":
                 with torch.cuda.stream(comm):
                     comm.wait_event(rendered)
                     if gather == "nccl":
@@ -631,10 +665,7 @@ def run_ours(args):
                 if i >= 0:
                     gev[i][1].record(stream)
                 rendered = torch.cuda.Event(); rendered.record(stream)
-            with torch.cuda.stream(comm):
-                comm.wait_event(rendered)
-                dist.all_reduce(token)               # "all stores of this step have landed"
-                done = torch.cuda.Event(); done.record(comm)
+            done = completion(i + 3 * NBUF, stream, rendered)      # "all stores of this step have landed" (i starts at -3; slots stay aligned)
             stream.wait_event(done)
         torch.cuda.synchronize(); dist.barrier()
         tg = torch.tensor([sum(a.elapsed_time(b) for a, b in gev) / 1e3], dtype=torch.float64, device="cuda")
@@ -770,7 +801,7 @@ def run_ours(args):
             ("ONE frame per step split into 16-row bands dealt round-robin over the ranks" if strong else
              "one frame per GPU per step (pose batch): independent units, no data-path collective - every frame stays in (and, in the e2e leg, goes to the host from) the GPU that rendered it")
             + ", grid replicated; gather: " + {"p2p": "every rank's render kernel stores its pixels straight into rank 0's frame over NVLink (CUDA IPC mapping), "
-                                                      "4-byte NCCL all-reduce per step as the completion signal (overlapped)",
+                                                      "completion signal per step: " + ("a counter in rank 0's memory that every rank's stream adds to after its render and rank 0's stream waits on (no collective)" if args.signal == "flag" else "4-byte NCCL all-reduce (overlapped)"),
                                                "dma": "every rank renders into its own memory; a copy-engine transfer on a side stream (cudaMemcpy2DAsync into rank 0's frame, CUDA IPC mapping) "
                                                       "follows inside the step window and overlaps the next frame's render in the pipelined pass",
                                                "nccl": "all_gather_into_tensor after the render, inside the step window",
@@ -841,7 +872,7 @@ def run_ours(args):
             "gathered": None if not gathered_pass else {
                 "value": rays_all / gathered_pass["t"] / 1e6, "unit": "Mrays/s", "ms_per_step": 1e3 * gathered_pass["t"] / args.steps,
                 "what": "second pass of the same K steps: every rank's render kernel stores its frame straight into rank 0's memory over NVLink (fused "
-                        "render + gather, %s), 4-byte NCCL all-reduce per step as the completion signal; bound by what ONE GPU can ingest" % ("packed RGB8" if gbpp == 3 else "RGBA8"),
+                        "render + gather, %s), completion signal per step (--signal %s); bound by what ONE GPU can ingest" % ("packed RGB8" if gbpp == 3 else "RGBA8", args.signal),
                 "bytes_into_rank0_per_step": (world - 1) * frame_bytes, "achieved_gbs": (world - 1) * frame_bytes * args.steps / gathered_pass["t"] / 1e9,
                 "ingest_peak_gbs": ingest_peak_gbs, "check": "ok" if gathered_pass["ok"] else "MISMATCH"},
             "gather": None if not ipc else {

@@ -266,6 +266,16 @@ int vrt_temporal_filter(vrt_ctx* ctx, const void* d_new_rgba8, const void* d_old
 int vrt_ipc_alloc_frame(vrt_ctx* ctx, size_t bytes, void** d_ptr, uint8_t handle[VRT_IPC_HANDLE_BYTES]);
 int vrt_ipc_open(vrt_ctx* ctx, const uint8_t handle[VRT_IPC_HANDLE_BYTES], void** d_ptr);
 int vrt_ipc_close(vrt_ctx* ctx, void* d_ptr);
+/* Completion flag of the fused render + gather, without a collective library or a host round trip.  A rank whose render stored into
+ * another GPU's frame calls vrt_signal_add on the same stream right after it: a one-thread kernel that fences at system scope and adds
+ * `value` to the 32-bit counter (which lives in the frame owner's memory, e.g. behind the frame in the vrt_ipc_alloc_frame allocation,
+ * zeroed by the owner).  The owner calls vrt_stream_wait_value: work submitted to `stream` afterwards starts once counter >= value
+ * (cuStreamWaitValue32; no SM is occupied while waiting).  Counters only grow: with N writers the k-th frame of a slot is complete at
+ * k * N.  Ordering rule: a process that both adds and waits enqueues its own add BEFORE its wait, and puts nothing behind the wait that
+ * another stream of the same process needs in order to produce an add - streams can share a hardware queue, and work queued behind a
+ * blocked wait never starts.  No counterpart in the reference (one GPU, one GL context). */
+int vrt_signal_add(vrt_ctx* ctx, void* d_counter, uint32_t value, void* stream);
+int vrt_stream_wait_value(vrt_ctx* ctx, void* d_counter, uint32_t value, void* stream);
 
 /* ---- host-side scene/camera helpers (no GPU needed) ----
  * Stand-ins for the parts of the un-vendored Greet engine that feed the path, with the conventions

@@ -183,3 +183,37 @@ def test_read_bandwidth_probe(ctx):
     assert hbm < l2 < 40000.0
     with pytest.raises(vrt.VrtError):
         ctx.probe_read_gbs(1024, 1)
+
+
+def test_signal_add_and_stream_wait_value(ctx):
+    """The completion flag of the fused gather, on one GPU.  (1) vrt_signal_add adds at system scope; a wait for a value already reached
+    lets the stream through.  (2) A wait on a counter that has NOT been reached blocks the stream's later work until the counter gets
+    there - released here by a HOST write to a pinned counter, not by a kernel on another stream: two streams may share a hardware queue,
+    and a kernel queued behind a blocked wait would never run (the ordering rule in include/vrt.h)."""
+    import time
+    import torch
+    d = ctx.device_alloc(256)
+    try:
+        ctx.device_memset(d, 0, 256)
+        ctx.synchronize()
+        st = torch.cuda.Stream()
+        for _ in range(3):
+            ctx.signal_add(d, 1, st.cuda_stream)
+        ctx.stream_wait_value(d, 3, st.cuda_stream)          # enqueued AFTER the adds it waits for
+        st.synchronize()
+        assert int(ctx.copy_to_host(d, 4).view(np.uint32)[0]) == 3
+        with pytest.raises(vrt.VrtError):
+            ctx.signal_add(d.value + 2, 1)                   # misaligned
+        host, hp = ctx.host_alloc(64)
+        flag = host.view(np.uint32)
+        flag[:] = 0
+        waiter = torch.cuda.Stream()
+        ctx.stream_wait_value(hp, 5, waiter.cuda_stream)
+        ctx.signal_add(d, 10, waiter.cuda_stream)            # behind the wait
+        time.sleep(0.05)
+        assert not waiter.query()                            # blocked: the counter is 0
+        flag[0] = 5                                          # the host releases it
+        waiter.synchronize()
+        assert int(ctx.copy_to_host(d, 4).view(np.uint32)[0]) == 13
+    finally:
+        ctx.device_free(d)

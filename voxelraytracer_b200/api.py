@@ -32,7 +32,7 @@ EXPORTS = [
     "vrt_framebuffer_device", "vrt_read_framebuffer", "vrt_read_debug_maps", "vrt_read_float_frame", "vrt_reset_counters",
     "vrt_get_counters", "vrt_last_render_ms", "vrt_kernel_launches", "vrt_grid_info_get", "vrt_read_cells", "vrt_read_sun_cells", "vrt_repack_static", "vrt_set_option",
     "vrt_host_alloc", "vrt_host_free", "vrt_device_alloc", "vrt_device_free", "vrt_synchronize", "vrt_copy_to_host", "vrt_copy_to_host_async", "vrt_copy_2d_async", "vrt_copy_to_device", "vrt_temporal_blend", "vrt_temporal_filter",
-    "vrt_ipc_alloc_frame", "vrt_ipc_open", "vrt_ipc_close", "vrt_scene_fill", "vrt_noise_heightmap", "vrt_atlas_synthetic",
+    "vrt_ipc_alloc_frame", "vrt_ipc_open", "vrt_ipc_close", "vrt_signal_add", "vrt_stream_wait_value", "vrt_scene_fill", "vrt_noise_heightmap", "vrt_atlas_synthetic",
     "vrt_atlas_pack", "vrt_camera_invpv", "vrt_sun_dir", "vrt_write_png",
 ]
 
@@ -154,6 +154,8 @@ def _signatures():
         "vrt_ipc_alloc_frame": (i32, [vp, C.c_size_t, C.POINTER(vp), vp]),
         "vrt_ipc_open": (i32, [vp, vp, C.POINTER(vp)]),
         "vrt_ipc_close": (i32, [vp, vp]),
+        "vrt_signal_add": (i32, [vp, vp, u32, vp]),
+        "vrt_stream_wait_value": (i32, [vp, vp, u32, vp]),
         "vrt_scene_fill": (i32, [i32, i32, vp, i32, u32, vp]),
         "vrt_noise_heightmap": (i32, [i32, u32, i32, f32, vp]),
         "vrt_atlas_synthetic": (i32, [i32, u32, vp]),
@@ -454,6 +456,12 @@ class Context:
         h = (C.c_uint8 * 64).from_buffer_copy(handle)
         self._check(self.lib.vrt_ipc_open(self.h, h, C.byref(p)))
         return p
+
+    def signal_add(self, d_counter, value, stream=None):
+        self._check(self.lib.vrt_signal_add(self.h, d_counter, value, stream))
+
+    def stream_wait_value(self, d_counter, value, stream=None):
+        self._check(self.lib.vrt_stream_wait_value(self.h, d_counter, value, stream))
 
     def ipc_close(self, p):
         self._check(self.lib.vrt_ipc_close(self.h, p))

@@ -43,4 +43,17 @@ cudaError_t launch_temporal_blend(const uint8_t* d_new, const uint8_t* d_old, ui
   return cudaGetLastError();
 }
 
+// Completion flag of the fused render + gather (vrt_signal_add): launched on the stream of a render whose stores went into another
+// GPU's memory; when it runs, that kernel has completed, the fence orders its stores before the system-scope add that the owner of the
+// frame waits on (vrt_stream_wait_value).  One thread.
+__global__ void signal_add_kernel(unsigned int* counter, unsigned int value) {
+  __threadfence_system();
+  atomicAdd_system(counter, value);
+}
+
+cudaError_t launch_signal_add(unsigned int* d_counter, unsigned int value, cudaStream_t s) {
+  signal_add_kernel<<<1, 1, 0, s>>>(d_counter, value);
+  return cudaGetLastError();
+}
+
 }  // namespace vrt

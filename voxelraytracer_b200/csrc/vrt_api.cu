@@ -687,6 +687,37 @@ int vrt_copy_to_device(vrt_ctx* ctx, void* d_dst, const void* host, size_t bytes
   return VRT_OK;
 }
 
+int vrt_signal_add(vrt_ctx* ctx, void* d_counter, uint32_t value, void* stream) {
+  if (!ctx || !d_counter || ((uintptr_t)d_counter & 3)) return fail(ctx, VRT_E_INVALID, "vrt_signal_add: counter must be a 4-byte aligned device address");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  CU(launch_signal_add((unsigned int*)d_counter, value, (cudaStream_t)stream));
+  ctx->launches += 1;
+  return VRT_OK;
+}
+
+int vrt_stream_wait_value(vrt_ctx* ctx, void* d_counter, uint32_t value, void* stream) {
+  if (!ctx || !d_counter || ((uintptr_t)d_counter & 3)) return fail(ctx, VRT_E_INVALID, "vrt_stream_wait_value: counter must be a 4-byte aligned device address");
+  int rc = bind(ctx);
+  if (rc) return rc;
+  // cuStreamWaitValue32(stream, addr, value, CU_STREAM_WAIT_VALUE_GEQ) through the driver entry point (libvrt links no libcuda): the
+  // stream's later work starts once *addr >= value; no SM is occupied while it waits
+  typedef int (*wait_fn)(cudaStream_t, unsigned long long, unsigned int, unsigned int);
+  static wait_fn fn = nullptr;
+  if (!fn) {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &f, cudaEnableDefault, &qr) != cudaSuccess || !f) {
+      cudaGetLastError();
+      return fail(ctx, VRT_E_CUDA, "vrt_stream_wait_value: cuStreamWaitValue32 is not available from this driver");
+    }
+    fn = (wait_fn)f;
+  }
+  const int r = fn((cudaStream_t)stream, (unsigned long long)(uintptr_t)d_counter, value, 0u /* GEQ */);
+  if (r != 0) return fail(ctx, VRT_E_CUDA, "vrt_stream_wait_value: cuStreamWaitValue32 failed with CUresult %d", r);
+  return VRT_OK;
+}
+
 int vrt_ipc_alloc_frame(vrt_ctx* ctx, size_t bytes, void** d_ptr, uint8_t handle[VRT_IPC_HANDLE_BYTES]) {
   if (!ctx || !d_ptr || !handle) return fail(ctx, VRT_E_INVALID, "vrt_ipc_alloc_frame: NULL argument");
   static_assert(sizeof(cudaIpcMemHandle_t) <= VRT_IPC_HANDLE_BYTES, "handle size");

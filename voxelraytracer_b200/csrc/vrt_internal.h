@@ -32,6 +32,7 @@ cudaError_t launch_sun_field(const uint16_t* d_base, uint16_t* d_out, int n, con
 
 // temporal.cu
 cudaError_t launch_read_probe(const void* d_buf, size_t bytes, int passes, int num_sms, unsigned int* sink, cudaStream_t stream);
+cudaError_t launch_signal_add(unsigned int* d_counter, unsigned int value, cudaStream_t stream);
 cudaError_t launch_temporal_blend(const uint8_t* d_new, const uint8_t* d_old, uint8_t* d_out, int64_t npix, float alpha, cudaStream_t stream);
 
 }  // namespace vrt
