@@ -1,0 +1,13 @@
+#!/bin/bash
+TR="timeout 250 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29518"
+$TR bench.py --gpus 8 --steps 120 --warmup 10 --workload c4 --scaling strong > gpurun_out/r02_bench_n8_c4s_flag.json 2> gpurun_out/r02_bench_n8_c4s_flag.err; echo rc=$?
+python - <<'PY'
+import json
+for f in ("r02_bench_n8_c4s_flag",):
+    try:
+        d = json.load(open("gpurun_out/%s.json" % f)); g = d.get("gather") or {}
+        print(f, "value %.0f ms %.4f median %.4f min %.4f kernel %.4f | pipelined %.0f = %.4f ms per frame | gather %.0f GB/s pipelined %.0f | e2e %.0f | check %s" % (
+            d["value"], d["ms_per_step"], d["ms_per_step_median"], d["ms_per_step_min"], d["kernel_ms_per_launch"], d["pipelined"]["value"], 1e3 / d["pipelined"]["frames_per_s"], g.get("achieved_gbs") or 0, g.get("pipelined_gbs") or 0, d["e2e"]["value"], d["gather_check"]))
+    except Exception as e:
+        print(f, "FAILED", e); print(open("gpurun_out/%s.err" % f).read()[-2000:])
+PY
