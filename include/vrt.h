@@ -73,6 +73,13 @@ enum {
                                     * (1024^3 chunks) the shader's `rayLength += tMin` accumulates ~1e-3 cells of error, and the skipping
                                     * walk - which does not accumulate - disagrees with it on ~0.03 % of the pixels instead of < 0.01 %. */
 
+#define VRT_FLAG_RAY_QUEUE  0x200u /* secondary rays through a warp-level queue: the bounce rays of a warp's 32 pixels are compacted (ballot + popc)
+                                    * and dealt to all 32 lanes every round instead of being walked serially by the thread that owns the pixel; results
+                                    * are composited per pixel in the shader's LIFO order (voxel.glsl:434-449), so the frame is byte-identical.  Used
+                                    * for frames of the lean kernel with glass in the chunk and maxReflections <= 1, maxTransparencies <= 2 (the
+                                    * reference's limits, voxel.glsl:4-5); ignored otherwise.  Off by default: measured slower on the named scenes,
+                                    * where 29-31 of a warp's 32 lanes are busy anyway. */
+
 #define VRT_HIT_MISS 0xFFFFFFFFu
 
 /* Per-frame inputs == the uniforms AppScene::Render() sets (src/main.cpp:333-348; declared at

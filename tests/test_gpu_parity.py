@@ -448,3 +448,29 @@ def test_persistent_launch_writes_the_same_pixels(ctx):
         assert np.array_equal(a, b)
         q = p.copy(); q.tile_x0, q.tile_y0, q.tile_w, q.tile_h = 37, 11, 300, 201
         assert np.array_equal(gpu_render(ctx, q, flags_extra=0).rgba8, gpu_render(ctx, q, flags_extra=vrt.FLAG_PERSISTENT).rgba8)
+
+
+def test_ray_queue_frames_are_byte_identical(ctx):
+    """VRT_FLAG_RAY_QUEUE (K3): a warp's bounce rays dealt to all 32 lanes by ballot + popc compaction, node results composited per
+    pixel in the shader's LIFO order - the frame must equal the serial per-pixel loop's byte for byte, on every launch shape; the flag
+    is ignored (same frame again) outside the (1, 2) bounce limits, without glass in the chunk and in the careful kernel."""
+    from voxelraytracer_b200 import sharding
+    for sc, pose, fl, W, H in (("refraction128", "refraction_close", 0, 1920, 1080), ("terrain128_glass", "glass_wall", 0, 1001, 563),
+                               ("terrain128_glass", "terrain_inside", 0, 960, 540), ("glass_cube32", "start", vrt.FLAG_COLOR_ONLY, 400, 400),
+                               ("glass_cube32", "start", 0, 333, 77), ("terrain32", "terrain32_above", 0, 17, 5)):
+        grid, n, atlas, ts = upload(ctx, sc)
+        p = make_params(W, H, sc, pose, fl)
+        q = p.copy(); q.flags |= vrt.FLAG_RAY_QUEUE
+        a = gpu_render(ctx, p, flags_extra=0).rgba8
+        assert np.array_equal(gpu_render(ctx, q, flags_extra=0).rgba8, a), (sc, pose, "full frame")
+        assert np.array_equal(gpu_render(ctx, q, flags_extra=vrt.FLAG_RGB8_OUT).rgba8, a[:, :3]), (sc, pose, "rgb8: staged store path")
+        pb = sharding.band_params(p, 1, 3, 16); qb = pb.copy(); qb.flags |= vrt.FLAG_RAY_QUEUE
+        assert np.array_equal(gpu_render(ctx, qb, flags_extra=0).rgba8, gpu_render(ctx, pb, flags_extra=0).rgba8), (sc, pose, "bands")
+        for refl, trans in ((0, 0), (1, 0), (0, 2), (1, 1), (2, 2), (3, 4)):            # within and beyond the queue's limits
+            r = p.copy(); r.maxReflections, r.maxTransparencies = refl, trans
+            rq = r.copy(); rq.flags |= vrt.FLAG_RAY_QUEUE
+            assert np.array_equal(gpu_render(ctx, rq, flags_extra=0).rgba8, gpu_render(ctx, r, flags_extra=0).rgba8), (sc, pose, refl, trans)
+    grid, n, atlas, ts = upload(ctx, "terrain128")                                       # no glass: flag ignored
+    p = make_params(640, 360, "terrain128", "terrain_low")
+    q = p.copy(); q.flags |= vrt.FLAG_RAY_QUEUE
+    assert np.array_equal(gpu_render(ctx, q, flags_extra=0).rgba8, gpu_render(ctx, p, flags_extra=0).rgba8)

@@ -12,8 +12,8 @@ from voxelraytracer_b200 import build_library
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OBJ = os.path.join(ROOT, "voxelraytracer_b200", "csrc", "kernels.o")
 CUOBJDUMP = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
-# render_kernel<FastTracer<FLAT=0, COUNT=0, NOISE=0, GLASS=g>, FLAT=0, DEBUG=0, 2, 2, DIRECT=1>: the kernels bench.py times at C2 (g=0) and C3/C4 (g=1)
-KERNEL = "_ZN3vrt13render_kernelINS_10FastTracerILb0ELb0ELb0ELb%dEEELb0ELb0ELi2ELi2ELb1EEEvNS_9FrameArgsE"
+# render_kernel<FastTracer<FLAT=0, COUNT=0, NOISE=0, GLASS=g>, FLAT=0, DEBUG=0, 2, 2, DIRECT=1, QUEUE=0>: the kernels bench.py times at C2 (g=0) and C3/C4 (g=1)
+KERNEL = "_ZN3vrt13render_kernelINS_10FastTracerILb0ELb0ELb0ELb%dEEELb0ELb0ELi2ELi2ELb1ELb0EEEvNS_9FrameArgsE"
 
 pytestmark = pytest.mark.skipif(not os.path.exists(CUOBJDUMP), reason="cuobjdump not available")
 

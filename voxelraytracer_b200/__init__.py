@@ -17,6 +17,7 @@ from .api import (  # noqa: F401
     FLAG_FLOAT_OUT,
     FLAG_OUT_FRAME,
     FLAG_PERSISTENT,
+    FLAG_RAY_QUEUE,
     FLAG_RGB8_OUT,
     HIT_MISS,
     OPT_OCTANT_FIELDS,

@@ -15,6 +15,7 @@ FLAG_OUT_FRAME = 0x20
 FLAG_PERSISTENT = 0x40
 FLAG_RGB8_OUT = 0x80
 FLAG_CAREFUL = 0x100
+FLAG_RAY_QUEUE = 0x200
 OPT_OCTANT_FIELDS = 1
 OPT_RADIUS_CAP = 2
 OPT_HOST_DIRECT = 3

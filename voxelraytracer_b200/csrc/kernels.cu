@@ -32,13 +32,16 @@ __device__ __forceinline__ size_t colour_index(const FrameArgs& f, int lx, int l
 
 // STAGED: the quantised colour is returned through *staged instead of being stored (the CTA-wide kernel transposes
 // it through shared memory so that every warp stores one full 128-byte row segment).
-template <class Tracer, bool FLAT, bool DEBUG, bool STAGED>
+// QUEUE: the warp shares its pixels' bounce rays (shade_pixel_queue, rt_shade.cuh); every lane takes part, with or without a pixel.
+template <class Tracer, bool FLAT, bool DEBUG, bool STAGED, bool QUEUE = false>
 __device__ __forceinline__ void render_one(const FrameArgs& f, int lx, int ly, uchar4* staged = nullptr) {
   typename Tracer::Ctx cx(f);
   const bool live = lx < f.p.tile_w && ly < f.rows_local;
+  PixelResult r;
+  if (QUEUE) r = shade_pixel_queue<Tracer, FLAT>(cx, f.p.tile_x0 + lx, live ? frame_row(f, ly) : 0, live);
   if (live) {
     const int px = f.p.tile_x0 + lx, py = frame_row(f, ly);
-    PixelResult r = shade_pixel<Tracer, FLAT>(cx, px, py);
+    if (!QUEUE) r = shade_pixel<Tracer, FLAT>(cx, px, py);
     const size_t o = (size_t)ly * (size_t)f.p.tile_w + (size_t)lx;                         // compact tile position
     uchar4 q;
     q.x = quantize_unorm8(r.rgba[0]); q.y = quantize_unorm8(r.rgba[1]); q.z = quantize_unorm8(r.rgba[2]); q.w = 255;
@@ -76,7 +79,7 @@ constexpr int min_ctas(int warps) { return VRT_MIN_BLOCKS * 4 / warps > 32 ? 32 
 // DIRECT: every thread stores its own pixel (frames in this GPU's own memory as RGBA8: a warp's 8x4 patch is four 32-byte row pieces,
 // i.e. four fully used DRAM sectors per store instruction) - no shared-memory stage, no CTA barrier, a warp that is done retires
 // instead of waiting for the slowest of the four (C2 0.0665 -> 0.0642 ms, profiles/r02_ab_direct_store_packed_stack.txt).
-template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY, bool DIRECT>
+template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY, bool DIRECT, bool QUEUE = false>
 __global__ void __launch_bounds__(WX * WY * 32, min_ctas(WX * WY)) render_kernel(const __grid_constant__ FrameArgs f) {
   constexpr int CW = kWarpW * WX, CH = kWarpH * WY;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -88,10 +91,10 @@ __global__ void __launch_bounds__(WX * WY * 32, min_ctas(WX * WY)) render_kernel
   __shared__ uchar4 patch[CH][CW];
   uchar4 q = make_uchar4(0, 0, 0, 255);
   if (DIRECT) {
-    render_one<Tracer, FLAT, DEBUG, false>(f, lx, ly);
+    render_one<Tracer, FLAT, DEBUG, false, QUEUE>(f, lx, ly);
     return;
   }
-  render_one<Tracer, FLAT, DEBUG, true>(f, lx, ly, &q);
+  render_one<Tracer, FLAT, DEBUG, true, QUEUE>(f, lx, ly, &q);
   patch[ly - by * CH][lx - blockIdx.x * CW] = q;
   __syncthreads();
   const int sx = threadIdx.x % CW, sy = threadIdx.x / CW;
@@ -161,26 +164,27 @@ cudaError_t launch_render_persistent(const FrameArgs& a, bool flat, bool glass, 
   return flat ? launch_fast_persistent<true>(a, glass, ticket, num_sms, s) : launch_fast_persistent<false>(a, glass, ticket, num_sms, s);
 }
 
-template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY>
+template <class Tracer, bool FLAT, bool DEBUG, int WX, int WY, bool QUEUE = false>
 static cudaError_t launch_variant(const FrameArgs& a, cudaStream_t s) {
   constexpr int CW = kWarpW * WX, CH = kWarpH * WY;
   dim3 grid((unsigned)((a.p.tile_w + CW - 1) / CW), (unsigned)((a.rows_local + CH - 1) / CH));
   if (grid.x == 0 || grid.y == 0) return cudaSuccess;
   // packed RGB8 rows and remote targets (4 x 1 arrangement, full 128-byte rows) go through the shared-memory transpose
-  if (WX == 2 && !(a.p.flags & VRT_FLAG_RGB8_OUT)) render_kernel<Tracer, FLAT, DEBUG, WX, WY, true><<<grid, WX * WY * 32, 0, s>>>(a);
-  else render_kernel<Tracer, FLAT, DEBUG, WX, WY, false><<<grid, WX * WY * 32, 0, s>>>(a);
+  if (WX == 2 && !(a.p.flags & VRT_FLAG_RGB8_OUT)) render_kernel<Tracer, FLAT, DEBUG, WX, WY, true, QUEUE><<<grid, WX * WY * 32, 0, s>>>(a);
+  else render_kernel<Tracer, FLAT, DEBUG, WX, WY, false, QUEUE><<<grid, WX * WY * 32, 0, s>>>(a);
   return cudaGetLastError();
 }
 
 // Picks the instantiation of the timed (fast, no debug attachments) kernel: shading variant, CTA arrangement, and the two
 // specialisations that drop code a frame cannot reach (NOISE: rt_shade.cuh; GLASS: no voxel of material 2 in the chunk).
 template <bool FLAT, bool DEBUG, int WX, int WY>
-static cudaError_t launch_fast(const FrameArgs& a, bool careful, bool glass, cudaStream_t s) {
+static cudaError_t launch_fast(const FrameArgs& a, bool careful, bool glass, cudaStream_t s, bool queue = false) {
+  if (!DEBUG && queue && glass && !careful) return launch_variant<FastTracer<FLAT, false, false, true>, FLAT, false, WX, WY, true>(a, s);   // K3
   if (careful) return glass ? launch_variant<FastTracer<FLAT, DEBUG, true, true>, FLAT, DEBUG, WX, WY>(a, s) : launch_variant<FastTracer<FLAT, DEBUG, true, false>, FLAT, DEBUG, WX, WY>(a, s);
   return glass ? launch_variant<FastTracer<FLAT, DEBUG, false, true>, FLAT, DEBUG, WX, WY>(a, s) : launch_variant<FastTracer<FLAT, DEBUG, false, false>, FLAT, DEBUG, WX, WY>(a, s);
 }
 
-cudaError_t launch_render(const FrameArgs& a, bool exact, bool flat, bool debug, bool wide_rows, bool glass, cudaStream_t s) {
+cudaError_t launch_render(const FrameArgs& a, bool exact, bool flat, bool debug, bool wide_rows, bool glass, bool queue, cudaStream_t s) {
   constexpr int LX = VRT_LOCAL_WX, LY = VRT_LOCAL_WY;
   if (exact) {
     if (flat) return debug ? launch_variant<ExactTracer<true, true>, true, true, 2, 2>(a, s) : launch_variant<ExactTracer<true, false>, true, false, 2, 2>(a, s);
@@ -191,8 +195,8 @@ cudaError_t launch_render(const FrameArgs& a, bool exact, bool flat, bool debug,
   // (debug) kernels are the same four instantiations with counters and attachments, so that what the tests look at is what is timed.
   const bool careful = a.careful != 0;
   if (debug) return flat ? launch_fast<true, true, 2, 2>(a, careful, glass, s) : launch_fast<false, true, 2, 2>(a, careful, glass, s);
-  if (wide_rows) return flat ? launch_fast<true, false, 4, 1>(a, careful, glass, s) : launch_fast<false, false, 4, 1>(a, careful, glass, s);
-  return flat ? launch_fast<true, false, LX, LY>(a, careful, glass, s) : launch_fast<false, false, LX, LY>(a, careful, glass, s);
+  if (wide_rows) return flat ? launch_fast<true, false, 4, 1>(a, careful, glass, s, queue) : launch_fast<false, false, 4, 1>(a, careful, glass, s, queue);
+  return flat ? launch_fast<true, false, LX, LY>(a, careful, glass, s, queue) : launch_fast<false, false, LX, LY>(a, careful, glass, s, queue);
 }
 
 }  // namespace vrt

@@ -130,7 +130,7 @@ struct Ray {
 
 // A bounce ray waiting on the per-pixel stack: what is read back, packed into 36 bytes (three vector accesses of local memory
 // instead of thirteen scalar ones).  medium is a voxel byte; the depths fit 8 bits (maxReflections + maxTransparencies <= 7, and the
-// transparency depth never drops below 0); face_axis is 0..2 for every bounce ray, face_nsign is +-1.
+// transparency depth never drops below 0); face_axis is -1 (the primary ray) or 0..2 and is stored + 1; face_nsign is +-1 where it matters.
 struct alignas(16) PackedRay {
   float px, py, pz, dx;
   float dy, dz, len, energy;
@@ -139,7 +139,7 @@ struct alignas(16) PackedRay {
 VRT_HD PackedRay pack_ray(const Ray& r) {
   PackedRay q;
   q.px = r.pos.x; q.py = r.pos.y; q.pz = r.pos.z; q.dx = r.dir.x; q.dy = r.dir.y; q.dz = r.dir.z; q.len = r.len; q.energy = r.energy;
-  q.bits = (uint32_t)(r.medium & 0xFF) | ((uint32_t)(r.nrefl & 0xFF) << 8) | ((uint32_t)(r.ntrans & 0xFF) << 16) | ((uint32_t)(r.face_axis & 3) << 24) |
+  q.bits = (uint32_t)(r.medium & 0xFF) | ((uint32_t)(r.nrefl & 0xFF) << 8) | ((uint32_t)(r.ntrans & 0xFF) << 16) | ((uint32_t)((r.face_axis + 1) & 3) << 24) |
            (r.face_nsign > 0.0f ? 0x4000000u : 0u);
   return q;
 }
@@ -147,7 +147,7 @@ VRT_HD Ray unpack_ray(const PackedRay& q) {
   Ray r;
   r.pos = mk3(q.px, q.py, q.pz); r.dir = mk3(q.dx, q.dy, q.dz); r.len = q.len; r.energy = q.energy;
   r.medium = (int)(q.bits & 0xFFu); r.nrefl = (int)((q.bits >> 8) & 0xFFu); r.ntrans = (int)(int8_t)((q.bits >> 16) & 0xFFu);
-  r.face_axis = (int)((q.bits >> 24) & 3u); r.face_nsign = (q.bits & 0x4000000u) ? 1.0f : -1.0f;
+  r.face_axis = (int)((q.bits >> 24) & 3u) - 1; r.face_nsign = (q.bits & 0x4000000u) ? 1.0f : -1.0f;
   return r;
 }
 

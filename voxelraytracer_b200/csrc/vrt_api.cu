@@ -378,7 +378,8 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   if ((p->flags & VRT_FLAG_PERSISTENT) && !debug && !(p->flags & (VRT_FLAG_EXACT | VRT_FLAG_RGB8_OUT))) {
     CU(launch_render_persistent(a, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, ctx->info.voxels_glass != 0, ctx->d_tickets + tm, ctx->num_sms, s));
   } else {
-    CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, ctx->opt_remote_rows && remote_target(ctx, d_out), ctx->info.voxels_glass != 0, s));
+    CU(launch_render(a, (p->flags & VRT_FLAG_EXACT) != 0, (p->flags & VRT_FLAG_COLOR_ONLY) != 0, debug, ctx->opt_remote_rows && remote_target(ctx, d_out), ctx->info.voxels_glass != 0,
+                     (p->flags & VRT_FLAG_RAY_QUEUE) != 0 && p->maxReflections <= 1 && p->maxTransparencies <= 2, s));
   }
   CU(cudaEventRecord(ctx->ev1[tm], s));
   ctx->launches += 1;

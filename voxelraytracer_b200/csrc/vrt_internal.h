@@ -10,7 +10,8 @@ namespace vrt {
 // kernels.cu: launches the per-pixel kernel variant selected by (exact, flat, debug).
 // grid/block are chosen inside; returns the cudaError of the launch.
 // wide_rows: 32x4-pixel CTAs storing full 128-byte rows (for frames in another GPU's memory) instead of 16x8-pixel CTAs.
-cudaError_t launch_render(const FrameArgs& args, bool exact, bool flat, bool debug, bool wide_rows, bool glass, cudaStream_t stream);
+// queue: VRT_FLAG_RAY_QUEUE applies (lean kernel, glass, bounce limits within (1, 2)): secondary rays go through the warp-level queue.
+cudaError_t launch_render(const FrameArgs& args, bool exact, bool flat, bool debug, bool wide_rows, bool glass, bool queue, cudaStream_t stream);
 // Persistent variant of the fast kernel: one CTA per SM slot pulling 8x4-pixel warp tiles from an atomic queue.
 cudaError_t launch_render_persistent(const FrameArgs& args, bool flat, bool glass, unsigned int* tile_counter, int num_sms, cudaStream_t stream);
 
