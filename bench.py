@@ -816,6 +816,10 @@ def run_ours(args):
         roof = {"bound": "issue", "unit": "Tinstr/s", "peak": p_issue / 1e12,
                 "achieved": ach_actual / 1e12 if nc else None, "frac": ach_actual / p_issue if nc else None,
                 "frac_actual": ach_actual / p_issue if nc else None,
+                "frac_frames_in_flight": (exec_per_launch / (t_pipeline / args.steps) / p_issue) if (nc and t_pipeline) else None,
+                "frac_frames_in_flight_def": "same executed thread-instructions over the time per frame of the `pipelined` pass (frames in flight on several streams, "
+                                             "no L2 fills): the launch latency, ramp-up and tail of one launch overlap the next, so this is what the kernel sustains; "
+                                             "`frac` is one isolated, L2-flushed launch",
                 "achieved_def": "thread-instructions the kernel EXECUTES per launch (ncu smsp__inst_executed x lanes per instruction, mean over the cycled poses) "
                                 "/ this run's CUDA-event time per launch",
                 "peak_source": "%d SM x 4 schedulers x 32 lanes x sampled SM clock %.0f MHz" % (sms, f_mhz),
