@@ -220,11 +220,11 @@ int vrt_repack_static(vrt_ctx* ctx, const void* d_voxels, int size, void* d_cell
 enum {
   VRT_OPT_OCTANT_FIELDS = 1, /* 1 (default) = eight direction-octant radius fields, 0 = one isotropic field */
   VRT_OPT_RADIUS_CAP = 2,    /* 1..255 = cap of the stored empty radius, 0 (default) = 255 up to 256^3, 96 above (build time is O(radius) per voxel) */
-  VRT_OPT_SUN_FIELD = 4,     /* the radius field the SHADOW rays walk: 1 (default) = for chunks up to 256^3 a field built for the frame's sun direction
-                                (every shadow ray points at the sun, voxel.glsl:191-201; one more (size+2)^3 uint16 array, built on the render stream on
-                                the second consecutive frame with the same u_SunDir - ~0.3 ms at 128^3 - so a sun that moves every frame, the
-                                reference's day / night cycle, never pays for it); 2 = for every chunk size, rebuilt at once whenever u_SunDir
-                                changes; 0 = shadow rays walk the sun's octant field.  Same pixels in every mode. */
+  VRT_OPT_SUN_FIELD = 4,     /* the radius field the SHADOW rays walk: 1 (default) = a field built for the frame's sun direction (every shadow ray points at
+                                the sun, voxel.glsl:191-201; one more (size+2)^3 uint16 array, built on the render stream on the second consecutive frame
+                                with the same u_SunDir - 0.3 ms at 128^3, 44 ms at 1024^3 - so a sun that moves every frame, the reference's day / night
+                                cycle, never pays for it; if the array cannot be allocated the octant field is walked and vrt_last_warning says so);
+                                2 = rebuilt at once whenever u_SunDir changes; 0 = shadow rays walk the sun's octant field.  Same pixels in every mode. */
   VRT_OPT_REMOTE_ROWS = 5,   /* 1 (default) = a colour target outside this GPU's memory (peer / IPC mapping, pinned host memory) is written by the 32x4-pixel CTA
                                 arrangement whose warps store whole 128-byte rows (what a bandwidth-bound link wants); 0 = by the same 16x8 arrangement with
                                 per-thread stores as local frames (no shared-memory stage, no CTA barrier: what a latency-bound small tile wants) */

@@ -30,7 +30,7 @@ struct vrt_ctx {
   int opt_radius_cap = 0;          // VRT_OPT_RADIUS_CAP, 0 = default by chunk size
   int opt_host_direct = 1;         // VRT_OPT_HOST_DIRECT
   int opt_remote_rows = 1;         // VRT_OPT_REMOTE_ROWS: remote targets get the 32x4 CTA arrangement that stores whole 128-byte rows
-  int opt_sun_field = 1;           // VRT_OPT_SUN_FIELD: 0 off, 1 auto (chunks up to 256^3, once the sun direction repeats), 2 always
+  int opt_sun_field = 1;           // VRT_OPT_SUN_FIELD: 0 off, 1 auto (built once the sun direction repeats), 2 always (built at once)
   float sun_seen[3] = {0, 0, 0};   // sun direction of the previous render (auto mode builds on the second frame in a row with the same one)
   uint16_t* d_sun = nullptr;       // the sun field (one more (n+2)^3 array), valid for sun_dir / sun_base
   float sun_dir[3] = {0, 0, 0};
@@ -347,7 +347,7 @@ static int render_impl(vrt_ctx* ctx, const vrt_params* p, uint8_t* d_out, cudaSt
   a.rows_local = (int)(npix / p->tile_w);
   finish_frame_args(a);
   // The sun field: rebuilt (on this stream, before the render) whenever the sun direction differs from the one it was built for.
-  if (!(p->flags & VRT_FLAG_EXACT) && (ctx->opt_sun_field == 2 || (ctx->opt_sun_field == 1 && ctx->size <= 256))) {
+  if (!(p->flags & VRT_FLAG_EXACT) && ctx->opt_sun_field != 0) {
     const uint16_t* base = a.sun_cells;                      // the sun octant's array (or the isotropic one)
     if (!ctx->d_sun) {
       const size_t p3 = (size_t)(ctx->size + 2) * (ctx->size + 2) * (ctx->size + 2);
